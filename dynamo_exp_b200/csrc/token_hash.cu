@@ -1,0 +1,629 @@
+// token_hash.cu — batched XXH3-64 token-block hashing on the GPU.
+//
+// Replaces the CPU hashing of the reference's token library and router indexer:
+//   block hash     lib/tokens/src/lib.rs:197-215  (TokenBlockChunk::new / from_tokens -> compute_hash :44-46)
+//   sequence hash  lib/tokens/src/lib.rs:238-261  (TokenBlock::from_chunk), chain loop :382-391
+//   split_tokens   lib/tokens/src/lib.rs:369-404  (rayon par_chunks_exact over blocks, serial chain)
+//   router hash    lib/llm/src/kv_router/indexer.rs:64,87-89,123-135 (seed 1337, un-chained)
+//   twin quirk     lib/llm/src/tokens.rs:126-144
+// The arithmetic is XXH3-64-with-seed (xxhash-rust 0.8.15 in the reference, a frozen public algorithm); it is
+// written here from the specification, not from any implementation's source.
+//
+// Launch structure for one ragged batch (CSR offsets):
+//   1. kvdp_block_count_scan_*  : block_offsets[r] = sum_{q<r} len_q / block_size       (3 tiny kernels)
+//   2. kvdp_hash_blocks_*       : one thread per token block. Fast path (256/512-byte blocks): each lane pulls its
+//                                 own block into a padded shared-memory row with one cp.async.bulk (TMA), so global
+//                                 reads are full-line and shared reads are conflict-free 16-byte loads; the seed-derived
+//                                 secret words arrive through the kernel-parameter constant bank.
+//   3. kvdp_hash_chain          : one thread per request walks its blocks (16-byte XXH3 per step, serial by nature).
+// HBM-bound by design: 4*block_size bytes read + 16 bytes written per block; no tensor cores (nothing contracts).
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+
+#include "common.cuh"
+
+namespace kvdp {
+namespace {
+
+// ------------------------------------------------------------------------------------------------ constants
+constexpr uint64_t P32_1 = 0x9E3779B1ULL, P32_2 = 0x85EBCA77ULL, P32_3 = 0xC2B2AE3DULL;
+constexpr uint64_t P64_1 = 0x9E3779B185EBCA87ULL, P64_2 = 0xC2B2AE3D27D4EB4FULL, P64_3 = 0x165667B19E3779F9ULL,
+                   P64_4 = 0x85EBCA77C2B2AE63ULL, P64_5 = 0x27D4EB2F165667C5ULL;
+constexpr uint64_t MX1 = 0x165667919E3779F9ULL, MX2 = 0x9FB21C651E98DF25ULL;
+
+// default 192-byte secret as 24 little-endian words
+#define KVDP_SECRET_WORDS                                                                                         \
+  {0xbe4ba423396cfeb8ULL, 0x1cad21f72c81017cULL, 0xdb979083e96dd4deULL, 0x1f67b3b7a4a44072ULL, 0x78e5c0cc4ee679cbULL, \
+   0x2172ffcc7dd05a82ULL, 0x8e2443f7744608b8ULL, 0x4c263a81e69035e0ULL, 0xcb00c391bb52283cULL, 0xa32e531b8b65d088ULL, \
+   0x4ef90da297486471ULL, 0xd8acdea946ef1938ULL, 0x3f349ce33f76faa8ULL, 0x1d4f0bc7c7bbdcf9ULL, 0x3159b4cd4be0518aULL, \
+   0x647378d9c97e9fc8ULL, 0xc3ebd33483acc5eaULL, 0xeb6313faffa081c5ULL, 0x49daf0b751dd0d17ULL, 0x9e68d429265516d3ULL, \
+   0xfca1477d58be162bULL, 0xce31d07ad1b8f88fULL, 0x280416958f3acb45ULL, 0x7e404bbbcafbd7afULL}
+
+__constant__ uint64_t c_secret[24] = KVDP_SECRET_WORDS;
+const uint64_t h_secret[24] = KVDP_SECRET_WORDS;
+
+// Seed-derived values handed to the kernels through the parameter constant bank.
+struct HashSecrets {
+  uint64_t w[24];    // custom-secret words: k[j] + seed (j even), k[j] - seed (j odd)
+  uint64_t last[8];  // rd64(S + 121 + 8l): secret of the final stripe
+  uint64_t fin[8];   // rd64(S + 11 + 8k): secret of the merge step
+  uint64_t flip16_lo;  // (k[3]^k[4]) + seed : 9..16-byte class
+  uint64_t flip16_hi;  // (k[5]^k[6]) - seed
+  uint64_t seed;
+};
+
+HashSecrets make_secrets(uint64_t seed) {
+  HashSecrets s;
+  for (int j = 0; j < 24; ++j) s.w[j] = (j & 1) ? h_secret[j] - seed : h_secret[j] + seed;
+  // unaligned reads of the byte string whose words are s.w: offset 121 = 15*8 + 1, offset 11 = 1*8 + 3
+  for (int l = 0; l < 8; ++l) s.last[l] = (s.w[15 + l] >> 8) | (s.w[16 + l] << 56);
+  for (int k = 0; k < 8; ++k) s.fin[k] = (s.w[1 + k] >> 24) | (s.w[2 + k] << 40);
+  s.flip16_lo = (h_secret[3] ^ h_secret[4]) + seed;
+  s.flip16_hi = (h_secret[5] ^ h_secret[6]) - seed;
+  s.seed = seed;
+  return s;
+}
+
+// ------------------------------------------------------------------------------------------------ device math
+__device__ __forceinline__ uint64_t rotl64(uint64_t x, int r) { return (x << r) | (x >> (64 - r)); }
+__device__ __forceinline__ uint32_t bswap32(uint32_t x) { return __byte_perm(x, 0, 0x0123); }
+__device__ __forceinline__ uint64_t bswap64(uint64_t x) {
+  return ((uint64_t)bswap32((uint32_t)x) << 32) | bswap32((uint32_t)(x >> 32));
+}
+__device__ __forceinline__ uint64_t fold128(uint64_t a, uint64_t b) { return (a * b) ^ __umul64hi(a, b); }
+__device__ __forceinline__ uint64_t avalanche(uint64_t h) {
+  h ^= h >> 37;
+  h *= MX1;
+  h ^= h >> 32;
+  return h;
+}
+__device__ __forceinline__ uint64_t xxh64_avalanche(uint64_t h) {
+  h ^= h >> 33;
+  h *= P64_2;
+  h ^= h >> 29;
+  h *= P64_3;
+  h ^= h >> 32;
+  return h;
+}
+__device__ __forceinline__ uint64_t rrmxmx(uint64_t h, uint64_t len) {
+  h ^= rotl64(h, 49) ^ rotl64(h, 24);
+  h *= MX2;
+  h ^= (h >> 35) + len;
+  h *= MX2;
+  h ^= h >> 28;
+  return h;
+}
+__device__ __forceinline__ uint64_t mul32x32(uint64_t k) { return (uint64_t)(uint32_t)k * (uint64_t)(uint32_t)(k >> 32); }
+
+// rd64 of the default secret at an arbitrary byte offset
+__device__ __forceinline__ uint64_t ksec64(uint32_t off) {
+  const uint32_t j = off >> 3, sh = (off & 7) * 8;
+  const uint64_t lo = c_secret[j];
+  if (sh == 0) return lo;
+  return (lo >> sh) | (c_secret[j + 1] << (64 - sh));
+}
+// rd64 of the seed-derived secret at an arbitrary byte offset
+__device__ __forceinline__ uint64_t dsec64(const HashSecrets& S, uint32_t off) {
+  const uint32_t j = off >> 3, sh = (off & 7) * 8;
+  const uint64_t lo = (j & 1) ? c_secret[j] - S.seed : c_secret[j] + S.seed;
+  if (sh == 0) return lo;
+  const uint64_t hi = ((j + 1) & 1) ? c_secret[j + 1] - S.seed : c_secret[j + 1] + S.seed;
+  return (lo >> sh) | (hi << (64 - sh));
+}
+
+// 16-byte class with both input words in registers: the chain step hash([parent, block_hash]).
+__device__ __forceinline__ uint64_t xxh3_16(uint64_t in0, uint64_t in1, const HashSecrets& S) {
+  const uint64_t lo = in0 ^ S.flip16_lo;
+  const uint64_t hi = in1 ^ S.flip16_hi;
+  return avalanche(16ULL + bswap64(lo) + hi + fold128(lo, hi));
+}
+
+// Byte readers for the generic path. WordReader needs 4-byte alignment of base and offsets (token data).
+struct ByteReader {
+  const uint8_t* p;
+  __device__ __forceinline__ uint32_t u8(uint32_t o) const { return p[o]; }
+  __device__ __forceinline__ uint32_t u32(uint32_t o) const {
+    return (uint32_t)p[o] | ((uint32_t)p[o + 1] << 8) | ((uint32_t)p[o + 2] << 16) | ((uint32_t)p[o + 3] << 24);
+  }
+  __device__ __forceinline__ uint64_t u64(uint32_t o) const { return (uint64_t)u32(o) | ((uint64_t)u32(o + 4) << 32); }
+};
+struct WordReader {
+  const uint32_t* p;
+  __device__ __forceinline__ uint32_t u8(uint32_t o) const { return (p[o >> 2] >> ((o & 3) * 8)) & 0xff; }
+  __device__ __forceinline__ uint32_t u32(uint32_t o) const { return p[o >> 2]; }
+  __device__ __forceinline__ uint64_t u64(uint32_t o) const {
+    return (uint64_t)p[o >> 2] | ((uint64_t)p[(o >> 2) + 1] << 32);
+  }
+};
+
+template <typename R>
+__device__ __forceinline__ uint64_t mix16(const R& in, uint32_t o, uint32_t so, uint64_t seed) {
+  return fold128(in.u64(o) ^ (ksec64(so) + seed), in.u64(o + 8) ^ (ksec64(so + 8) - seed));
+}
+
+template <typename R>
+__device__ __forceinline__ void accumulate_stripe(uint64_t acc[8], const R& in, uint32_t o, const HashSecrets& S,
+                                                  uint32_t so) {
+#pragma unroll
+  for (int l = 0; l < 8; l += 2) {
+    const uint64_t a0 = in.u64(o + 8 * l), a1 = in.u64(o + 8 * l + 8);
+    const uint64_t k0 = a0 ^ dsec64(S, so + 8 * l), k1 = a1 ^ dsec64(S, so + 8 * l + 8);
+    acc[l] += a1 + mul32x32(k0);
+    acc[l + 1] += a0 + mul32x32(k1);
+  }
+}
+
+// Every XXH3-64 length class, any length; the slow but complete path.
+template <typename R>
+__device__ uint64_t xxh3_generic(const R& in, uint32_t len, const HashSecrets& S) {
+  const uint64_t seed = S.seed;
+  if (len == 0) return xxh64_avalanche(seed ^ ksec64(56) ^ ksec64(64));
+  if (len <= 3) {
+    const uint32_t c1 = in.u8(0), c2 = in.u8(len >> 1), c3 = in.u8(len - 1);
+    const uint32_t comb = (c1 << 16) | (c2 << 24) | c3 | (len << 8);
+    const uint64_t flip = (uint64_t)((uint32_t)c_secret[0] ^ (uint32_t)(c_secret[0] >> 32)) + seed;
+    return xxh64_avalanche((uint64_t)comb ^ flip);
+  }
+  if (len <= 8) {
+    const uint64_t s2 = seed ^ ((uint64_t)bswap32((uint32_t)seed) << 32);
+    const uint64_t in64 = (uint64_t)in.u32(len - 4) + ((uint64_t)in.u32(0) << 32);
+    const uint64_t flip = (ksec64(8) ^ ksec64(16)) - s2;
+    return rrmxmx(in64 ^ flip, len);
+  }
+  if (len <= 16) {
+    const uint64_t lo = in.u64(0) ^ ((ksec64(24) ^ ksec64(32)) + seed);
+    const uint64_t hi = in.u64(len - 8) ^ ((ksec64(40) ^ ksec64(48)) - seed);
+    return avalanche((uint64_t)len + bswap64(lo) + hi + fold128(lo, hi));
+  }
+  if (len <= 128) {
+    uint64_t acc = (uint64_t)len * P64_1;
+    for (int i = (int)((len - 1) / 32); i >= 0; --i) {
+      acc += mix16(in, 16 * i, 32 * i, seed);
+      acc += mix16(in, len - 16 * (i + 1), 32 * i + 16, seed);
+    }
+    return avalanche(acc);
+  }
+  if (len <= 240) {
+    uint64_t acc = (uint64_t)len * P64_1;
+    for (int i = 0; i < 8; ++i) acc += mix16(in, 16 * i, 16 * i, seed);
+    acc = avalanche(acc);
+    uint64_t end = mix16(in, len - 16, 136 - 17, seed);
+    const int rounds = (int)(len / 16);
+    for (int i = 8; i < rounds; ++i) end += mix16(in, 16 * i, 16 * (i - 8) + 3, seed);
+    return avalanche(acc + end);
+  }
+  uint64_t acc[8] = {P32_3, P64_1, P64_2, P64_3, P64_4, P32_2, P64_5, P32_1};
+  const uint32_t nb_blocks = (len - 1) / 1024;
+  for (uint32_t b = 0; b < nb_blocks; ++b) {
+    for (uint32_t n = 0; n < 16; ++n) accumulate_stripe(acc, in, b * 1024 + 64 * n, S, 8 * n);
+#pragma unroll
+    for (int l = 0; l < 8; ++l) {
+      uint64_t a = acc[l];
+      a ^= a >> 47;
+      a ^= dsec64(S, 128 + 8 * l);
+      a *= P32_1;
+      acc[l] = a;
+    }
+  }
+  const uint32_t nb_stripes = ((len - 1) - 1024 * nb_blocks) / 64;
+  for (uint32_t n = 0; n < nb_stripes; ++n) accumulate_stripe(acc, in, nb_blocks * 1024 + 64 * n, S, 8 * n);
+  accumulate_stripe(acc, in, len - 64, S, 121);
+  uint64_t r = (uint64_t)len * P64_1;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) r += fold128(acc[2 * i] ^ dsec64(S, 11 + 16 * i), acc[2 * i + 1] ^ dsec64(S, 11 + 16 * i + 8));
+  return avalanche(r);
+}
+
+// ------------------------------------------------------------------------------------------------ block -> request
+// Largest r with block_offsets[r] <= gb, skipping zero-block requests so that gb < block_offsets[r+1].
+__device__ __forceinline__ int64_t find_request(const int64_t* __restrict__ block_offsets, int64_t n_req, int64_t gb0,
+                                                int64_t gb) {
+  // warp-uniform binary search for the first block of the warp's tile, then a short per-lane walk
+  int64_t lo = 0, hi = n_req;  // invariant: block_offsets[lo] <= gb0 < block_offsets[hi] (= total at n_req)
+  while (hi - lo > 1) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (__ldg(block_offsets + mid) <= gb0)
+      lo = mid;
+    else
+      hi = mid;
+  }
+  int64_t r = lo;
+  while (r + 1 < n_req && __ldg(block_offsets + r + 1) <= gb) ++r;
+  return r;
+}
+
+struct HashArgs {
+  const uint32_t* tokens;
+  const int64_t* offsets;        // [n_req+1] token offsets
+  const int64_t* block_offsets;  // [n_req+1] block offsets (scan result)
+  uint64_t* block_hash;
+  uint64_t* seq_hash;
+  int64_t n_req;
+  int32_t block_size;
+  uint32_t flags;
+};
+
+// ------------------------------------------------------------------------------------------------ fast block hash
+// LEN = 64*NSTRIPES bytes per block (256 for 64-token blocks, 512 for 128-token blocks).
+template <int NSTRIPES, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) kvdp_hash_blocks_tma(const __grid_constant__ HashArgs A,
+                                                                   const __grid_constant__ HashSecrets S) {
+  constexpr int LEN = 64 * NSTRIPES;
+  constexpr int ROW = LEN + 16;  // +16 B pad: 16-byte loads of 8 consecutive lanes hit 8 distinct bank groups
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* wbase = smem + (size_t)warp * (32 * ROW);
+  const uint32_t row = smem_u32(wbase) + lane * ROW;
+  const uint32_t bar = smem_u32(smem + (size_t)WARPS * 32 * ROW) + 8 * warp;
+  if (lane == 0) {
+    mbar_init(bar, 32);
+    mbar_fence_init();
+  }
+  __syncwarp();
+
+  const int64_t total = __ldg(A.block_offsets + A.n_req);
+  const int64_t tiles = (total + 31) >> 5;
+  uint32_t parity = 0;
+  for (int64_t t = (int64_t)blockIdx.x * WARPS + warp; t < tiles; t += (int64_t)gridDim.x * WARPS) {
+    const int64_t gb = t * 32 + lane;
+    const bool valid = gb < total;
+    if (valid) {
+      const int64_t r = find_request(A.block_offsets, A.n_req, t * 32, gb);
+      const uint32_t* src =
+          A.tokens + __ldg(A.offsets + r) + (gb - __ldg(A.block_offsets + r)) * (int64_t)A.block_size;
+      if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        mbar_expect_tx(bar, LEN);
+        bulk_g2s(row, src, LEN, bar);
+      } else {
+        // request does not start on a 16-byte boundary: this lane fills its row with 4-byte loads
+        uint32_t* dstw = reinterpret_cast<uint32_t*>(wbase + lane * ROW);
+        for (int i = 0; i < LEN / 4; ++i) dstw[i] = __ldg(src + i);
+        mbar_arrive(bar);
+      }
+    } else {
+      mbar_arrive(bar);
+    }
+    mbar_wait(bar, parity);
+    parity ^= 1;
+    if (valid) {
+      uint64_t acc[8] = {P32_3, P64_1, P64_2, P64_3, P64_4, P32_2, P64_5, P32_1};
+#pragma unroll
+      for (int n = 0; n < NSTRIPES; ++n) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int4 v = lds16(row + 64 * n + 16 * q);
+          const uint64_t a0 = (uint64_t)(uint32_t)v.x | ((uint64_t)(uint32_t)v.y << 32);
+          const uint64_t a1 = (uint64_t)(uint32_t)v.z | ((uint64_t)(uint32_t)v.w << 32);
+          const uint64_t s0 = (n == NSTRIPES - 1) ? S.last[2 * q] : S.w[n + 2 * q];
+          const uint64_t s1 = (n == NSTRIPES - 1) ? S.last[2 * q + 1] : S.w[n + 2 * q + 1];
+          acc[2 * q] += a1 + mul32x32(a0 ^ s0);
+          acc[2 * q + 1] += a0 + mul32x32(a1 ^ s1);
+        }
+      }
+      uint64_t h = (uint64_t)LEN * P64_1;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) h += fold128(acc[2 * i] ^ S.fin[2 * i], acc[2 * i + 1] ^ S.fin[2 * i + 1]);
+      A.block_hash[gb] = avalanche(h);
+    }
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ generic block hash
+__global__ void __launch_bounds__(256) kvdp_hash_blocks_generic(const __grid_constant__ HashArgs A,
+                                                                const __grid_constant__ HashSecrets S) {
+  const int64_t total = __ldg(A.block_offsets + A.n_req);
+  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t gb = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gb < total; gb += nthreads) {
+    const int64_t r = find_request(A.block_offsets, A.n_req, gb & ~(int64_t)31, gb);
+    WordReader in{A.tokens + __ldg(A.offsets + r) + (gb - __ldg(A.block_offsets + r)) * (int64_t)A.block_size};
+    A.block_hash[gb] = xxh3_generic(in, (uint32_t)A.block_size * 4u, S);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ chain
+__global__ void __launch_bounds__(128) kvdp_hash_chain(const __grid_constant__ HashArgs A,
+                                                       const __grid_constant__ HashSecrets S) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= A.n_req) return;
+  const int64_t b0 = __ldg(A.block_offsets + r), b1 = __ldg(A.block_offsets + r + 1);
+  uint64_t parent = 0;
+  for (int64_t b = b0; b < b1; ++b) {
+    const uint64_t bh = A.block_hash[b];
+    uint64_t sh;
+    if (b == b0 && !(A.flags & KVDP_HASH_TWIN_FIRST))
+      sh = bh;
+    else
+      sh = xxh3_16(parent, bh, S);
+    A.seq_hash[b] = sh;
+    parent = sh;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ block-count scan
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 16;  // requests per thread
+constexpr int kScanTile = kScanThreads * kScanItems;
+
+__device__ __forceinline__ int64_t req_blocks(const int64_t* __restrict__ offsets, int64_t r, int64_t n_req,
+                                              int32_t bs) {
+  if (r >= n_req) return 0;
+  const int64_t len = __ldg(offsets + r + 1) - __ldg(offsets + r);
+  return len > 0 ? len / bs : 0;
+}
+
+__device__ __forceinline__ int64_t block_exclusive_scan(int64_t v, int64_t* total, int64_t* warp_sums) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int64_t incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int64_t o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += o;
+  }
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int64_t w = lane < (kScanThreads / 32) ? warp_sums[lane] : 0;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int64_t o = __shfl_up_sync(0xffffffffu, w, d);
+      if (lane >= d) w += o;
+    }
+    if (lane < (kScanThreads / 32)) warp_sums[lane] = w;  // inclusive over warps
+  }
+  __syncthreads();
+  const int64_t warp_prefix = warp ? warp_sums[warp - 1] : 0;
+  *total = warp_sums[kScanThreads / 32 - 1];
+  return warp_prefix + incl - v;
+}
+
+__global__ void __launch_bounds__(kScanThreads) kvdp_block_count_scan_partials(const int64_t* __restrict__ offsets,
+                                                                               int64_t n_req, int32_t bs,
+                                                                               int64_t* __restrict__ partials) {
+  __shared__ int64_t warp_sums[kScanThreads / 32];
+  const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
+  int64_t s = 0;
+#pragma unroll
+  for (int i = 0; i < kScanItems; ++i) s += req_blocks(offsets, base + i, n_req, bs);
+  int64_t total;
+  block_exclusive_scan(s, &total, warp_sums);
+  if (threadIdx.x == 0) partials[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(kScanThreads) kvdp_block_count_scan_spine(int64_t* __restrict__ partials,
+                                                                            int64_t n_tiles) {
+  __shared__ int64_t warp_sums[kScanThreads / 32];
+  __shared__ int64_t carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (int64_t base = 0; base < n_tiles; base += kScanThreads) {
+    const int64_t i = base + threadIdx.x;
+    const int64_t v = i < n_tiles ? partials[i] : 0;
+    int64_t total;
+    const int64_t ex = block_exclusive_scan(v, &total, warp_sums);
+    const int64_t carry = carry_s;
+    if (i < n_tiles) partials[i] = carry + ex;
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s = carry + total;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(kScanThreads) kvdp_block_count_scan_apply(const int64_t* __restrict__ offsets,
+                                                                            int64_t n_req, int32_t bs,
+                                                                            const int64_t* __restrict__ partials,
+                                                                            int64_t* __restrict__ block_offsets) {
+  __shared__ int64_t warp_sums[kScanThreads / 32];
+  const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
+  int64_t v[kScanItems];
+  int64_t s = 0;
+#pragma unroll
+  for (int i = 0; i < kScanItems; ++i) {
+    v[i] = req_blocks(offsets, base + i, n_req, bs);
+    s += v[i];
+  }
+  int64_t total;
+  int64_t run = partials[blockIdx.x] + block_exclusive_scan(s, &total, warp_sums);
+#pragma unroll
+  for (int i = 0; i < kScanItems; ++i) {
+    if (base + i <= n_req) block_offsets[base + i] = run;  // entry n_req receives the grand total
+    run += v[i];
+  }
+}
+
+__global__ void kvdp_xxh3_batch_kernel(const uint8_t* __restrict__ data, int64_t n, int64_t len, uint64_t* out,
+                                       const __grid_constant__ HashSecrets S) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  ByteReader in{data + i * len};
+  out[i] = xxh3_generic(in, (uint32_t)len, S);
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+}  // namespace kvdp
+
+using namespace kvdp;
+
+extern "C" {
+
+size_t kvdp_hash_workspace_bytes(int64_t n_req) {
+  if (n_req < 0) n_req = 0;
+  const int64_t tiles = (n_req + 1 + kScanTile - 1) / kScanTile;
+  return align_up((size_t)(tiles + 1) * sizeof(int64_t), 256);
+}
+
+int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, int64_t n_req, int64_t total_tokens,
+                           int32_t block_size, uint64_t salt, int64_t* d_block_offsets, uint64_t* d_block_hash,
+                           uint64_t* d_seq_hash, void* d_workspace, size_t workspace_bytes, uint32_t flags,
+                           kvdp_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n_req < 0 || total_tokens < 0) return fail(KVDP_EINVAL, "hash: negative n_req/total_tokens");
+  if (block_size < 1) return fail(KVDP_EINVAL, "hash: block_size must be >= 1");
+  if (!d_offsets || !d_block_offsets) return fail(KVDP_EINVAL, "hash: NULL offsets / block_offsets");
+  if (total_tokens > 0 && !d_tokens) return fail(KVDP_EINVAL, "hash: NULL tokens");
+  if (flags & ~KVDP_HASH_TWIN_FIRST) return fail(KVDP_EINVAL, "hash: unknown flags 0x%x", flags);
+  const size_t need = kvdp_hash_workspace_bytes(n_req);
+  if (!d_workspace || workspace_bytes < need)
+    return fail(KVDP_EINVAL, "hash: workspace of %zu bytes needed, %zu given", need, workspace_bytes);
+  if ((uint64_t)block_size * 4 >= ((uint64_t)1 << 31)) return fail(KVDP_ERANGE, "hash: block_size too large");
+
+  int dev = 0;
+  KVDP_CUDA(cudaGetDevice(&dev));
+  DevInfo di;
+  if (int rc = device_info(dev, &di)) return rc;
+
+  // 1. block offsets
+  int64_t* partials = (int64_t*)d_workspace;
+  const int64_t tiles = (n_req + 1 + kScanTile - 1) / kScanTile;
+  kvdp_block_count_scan_partials<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size, partials);
+  kvdp_block_count_scan_spine<<<1, kScanThreads, 0, stream>>>(partials, tiles);
+  kvdp_block_count_scan_apply<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size, partials,
+                                                                            d_block_offsets);
+  KVDP_CUDA(cudaGetLastError());
+
+  const int64_t max_blocks = total_tokens / block_size;
+  if (max_blocks == 0 || n_req == 0) return 0;
+  if (!d_block_hash) return fail(KVDP_EINVAL, "hash: NULL block_hash");
+
+  HashArgs A;
+  A.tokens = d_tokens;
+  A.offsets = d_offsets;
+  A.block_offsets = d_block_offsets;
+  A.block_hash = d_block_hash;
+  A.seq_hash = d_seq_hash;
+  A.n_req = n_req;
+  A.block_size = block_size;
+  A.flags = flags;
+  const HashSecrets S = make_secrets(salt);
+
+  // 2. block hashes
+  const int len = block_size * 4;
+  const int64_t warp_tiles = (max_blocks + 31) / 32;
+  if (len == 256) {
+    constexpr int W = 8;
+    const size_t smem = (size_t)W * 32 * (256 + 16) + 8 * W;
+    static bool attr_set = false;
+    if (!attr_set) {
+      KVDP_CUDA(cudaFuncSetAttribute(kvdp_hash_blocks_tma<4, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+      attr_set = true;
+    }
+    const int64_t grid = std::min<int64_t>((warp_tiles + W - 1) / W, (int64_t)di.sm_count * 3);
+    kvdp_hash_blocks_tma<4, W><<<(unsigned)std::max<int64_t>(grid, 1), W * 32, smem, stream>>>(A, S);
+  } else if (len == 512) {
+    constexpr int W = 4;
+    const size_t smem = (size_t)W * 32 * (512 + 16) + 8 * W;
+    static bool attr_set = false;
+    if (!attr_set) {
+      KVDP_CUDA(cudaFuncSetAttribute(kvdp_hash_blocks_tma<8, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+      attr_set = true;
+    }
+    const int64_t grid = std::min<int64_t>((warp_tiles + W - 1) / W, (int64_t)di.sm_count * 3);
+    kvdp_hash_blocks_tma<8, W><<<(unsigned)std::max<int64_t>(grid, 1), W * 32, smem, stream>>>(A, S);
+  } else {
+    const int64_t grid = std::min<int64_t>((max_blocks + 255) / 256, (int64_t)di.sm_count * 8);
+    kvdp_hash_blocks_generic<<<(unsigned)std::max<int64_t>(grid, 1), 256, 0, stream>>>(A, S);
+  }
+  KVDP_CUDA(cudaGetLastError());
+
+  // 3. chain
+  if (d_seq_hash) {
+    kvdp_hash_chain<<<(unsigned)((n_req + 127) / 128), 128, 0, stream>>>(A, S);
+    KVDP_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+int kvdp_xxh3_64_batch(const uint8_t* d_data, int64_t n, int64_t len, uint64_t seed, uint64_t* d_out,
+                       kvdp_stream_t stream) {
+  if (n < 0 || len < 0 || len >= ((int64_t)1 << 31)) return fail(KVDP_EINVAL, "xxh3 batch: bad n/len");
+  if (n == 0) return 0;
+  if (!d_out || (len > 0 && !d_data)) return fail(KVDP_EINVAL, "xxh3 batch: NULL pointer");
+  const HashSecrets S = make_secrets(seed);
+  kvdp_xxh3_batch_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(d_data, n, len, d_out, S);
+  KVDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ host-buffer form
+namespace {
+struct HostHashCtx {
+  std::mutex mu;
+  cudaStream_t stream = nullptr;
+  void* d_tokens = nullptr;
+  size_t tok_cap = 0;
+  void* d_req = nullptr;  // offsets + block_offsets
+  size_t req_cap = 0;
+  void* d_out = nullptr;  // block_hash + seq_hash
+  size_t out_cap = 0;
+  void* d_ws = nullptr;
+  size_t ws_cap = 0;
+};
+HostHashCtx g_host_ctx[64];
+
+int ensure(void** p, size_t* cap, size_t need) {
+  if (*cap >= need) return 0;
+  if (*p) KVDP_CUDA(cudaFree(*p));
+  *p = nullptr;
+  *cap = 0;
+  const size_t sz = std::max(need, (size_t)1 << 20);
+  KVDP_CUDA(cudaMalloc(p, sz));
+  *cap = sz;
+  return 0;
+}
+}  // namespace
+
+int kvdp_hash_token_blocks_host(const uint32_t* h_tokens, const int64_t* h_offsets, int64_t n_req, int32_t block_size,
+                                uint64_t salt, int64_t* h_block_offsets, uint64_t* h_block_hash, uint64_t* h_seq_hash,
+                                uint32_t flags, int32_t device) {
+  if (n_req < 0 || !h_offsets || !h_block_offsets) return fail(KVDP_EINVAL, "hash(host): bad arguments");
+  if (block_size < 1) return fail(KVDP_EINVAL, "hash(host): block_size must be >= 1");
+  if (device < 0) KVDP_CUDA(cudaGetDevice(&device));
+  if (device >= 64) return fail(KVDP_EINVAL, "device ordinal %d not supported", device);
+  // validate offsets on the host (the device path trusts them)
+  int64_t total_blocks = 0;
+  for (int64_t r = 0; r < n_req; ++r) {
+    if (h_offsets[r + 1] < h_offsets[r]) return fail(KVDP_EINVAL, "hash(host): offsets must be non-decreasing");
+    total_blocks += (h_offsets[r + 1] - h_offsets[r]) / block_size;
+  }
+  const int64_t tok_begin = h_offsets[0], tok_end = h_offsets[n_req];
+  const int64_t total_tokens = tok_end;  // offsets index into h_tokens from 0
+  if (tok_begin < 0) return fail(KVDP_EINVAL, "hash(host): negative offset");
+  if (total_tokens > 0 && !h_tokens) return fail(KVDP_EINVAL, "hash(host): NULL tokens");
+  if (total_blocks > 0 && !h_block_hash) return fail(KVDP_EINVAL, "hash(host): NULL block_hash");
+
+  DeviceGuard g(device);
+  HostHashCtx& c = g_host_ctx[device];
+  std::lock_guard<std::mutex> lk(c.mu);
+  if (!c.stream) KVDP_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+  if (int rc = ensure(&c.d_tokens, &c.tok_cap, (size_t)total_tokens * 4 + 16)) return rc;
+  if (int rc = ensure(&c.d_req, &c.req_cap, (size_t)(n_req + 1) * 16)) return rc;
+  if (int rc = ensure(&c.d_out, &c.out_cap, (size_t)total_blocks * 16 + 16)) return rc;
+  const size_t ws = kvdp_hash_workspace_bytes(n_req);
+  if (int rc = ensure(&c.d_ws, &c.ws_cap, ws)) return rc;
+  int64_t* d_off = (int64_t*)c.d_req;
+  int64_t* d_boff = d_off + (n_req + 1);
+  uint64_t* d_bh = (uint64_t*)c.d_out;
+  uint64_t* d_sh = d_bh + total_blocks;
+  if (total_tokens > 0)
+    KVDP_CUDA(cudaMemcpyAsync(c.d_tokens, h_tokens, (size_t)total_tokens * 4, cudaMemcpyHostToDevice, c.stream));
+  KVDP_CUDA(cudaMemcpyAsync(d_off, h_offsets, (size_t)(n_req + 1) * 8, cudaMemcpyHostToDevice, c.stream));
+  if (int rc = kvdp_hash_token_blocks((const uint32_t*)c.d_tokens, d_off, n_req, total_tokens, block_size, salt, d_boff,
+                                      d_bh, h_seq_hash ? d_sh : nullptr, c.d_ws, c.ws_cap, flags, c.stream))
+    return rc;
+  KVDP_CUDA(cudaMemcpyAsync(h_block_offsets, d_boff, (size_t)(n_req + 1) * 8, cudaMemcpyDeviceToHost, c.stream));
+  if (total_blocks > 0) {
+    KVDP_CUDA(cudaMemcpyAsync(h_block_hash, d_bh, (size_t)total_blocks * 8, cudaMemcpyDeviceToHost, c.stream));
+    if (h_seq_hash)
+      KVDP_CUDA(cudaMemcpyAsync(h_seq_hash, d_sh, (size_t)total_blocks * 8, cudaMemcpyDeviceToHost, c.stream));
+  }
+  KVDP_CUDA(cudaStreamSynchronize(c.stream));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,243 @@
+"""V2 host API over libkvdp.so: copy plans, the transfer engine, contiguous-per-block slabs and the host tier.
+
+These are the batched counterparts of `CopyStreamBlockMap` / `CopyStream` (lib/llm/src/kv/layer.rs:592-979): one
+plan per (source set, destination set), one kernel launch per request covering all layers. The TP-reshard plan and the
+peer/flag helpers replace what the patched vLLM connector does with Triton + NIXL
+(container/deps/vllm/vllm_v0.8.4-dynamo-kv-disagg-patch.patch:934-1031, :1131-1186, :1361-1471).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from .layer import KvBlockStorage, KvLayout, _ids32
+from .storage import CudaPinnedMemory, DeviceStorageOwned, KvError, Storage, StorageType
+
+
+def _u64(ptrs) -> np.ndarray:
+    return np.ascontiguousarray(np.asarray(ptrs, dtype=np.uint64))
+
+
+class CopyPlan:
+    """Owner of a `kvdp_plan*`."""
+
+    def __init__(self, handle: C.c_void_p, keepalive=None):
+        self._h = handle
+        self._keep = keepalive
+
+    @property
+    def handle(self) -> C.c_void_p:
+        return self._h
+
+    def bytes_per_pair(self) -> int:
+        return int(_lib.lib().kvdp_plan_bytes_per_pair(self._h))
+
+    def close(self) -> None:
+        if self._h is not None and self._h.value:
+            _lib.lib().kvdp_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- constructors -------------------------------------------------------------------------------------
+    @classmethod
+    def block_copy(cls, src: KvBlockStorage, dst: KvBlockStorage, device: int = -1) -> "CopyPlan":
+        """Same-layout multi-layer block copy; the v2 form of `CopyStreamBlockMap::new` (kv/layer.rs:648-688)."""
+        if not src.block_details.is_compatible(dst.block_details):
+            raise KvError("src and dst must have compatible block details")
+        if len(src.layers) != len(dst.layers):
+            raise KvError("src and dst must have the same number of layers")
+        sp, dp = _u64(src.layer_pointers()), _u64(dst.layer_pointers())
+        h = C.c_void_p()
+        bd = src.block_details
+        _lib.check(_lib.lib().kvdp_plan_block_copy(C.byref(h), sp.ctypes.data, dp.ctypes.data, len(sp), bd.prefix_dim(),
+                                                   src.number_of_blocks(), dst.number_of_blocks(), bd.suffix_dim(),
+                                                   bd.elem_size(), device))
+        return cls(h, (src, dst))
+
+    @classmethod
+    def block_copy_raw(cls, src_ptrs, dst_ptrs, prefix_dim, src_block_dim, dst_block_dim, suffix_dim, elem_size,
+                       device: int = -1, keepalive=None) -> "CopyPlan":
+        sp, dp = _u64(src_ptrs), _u64(dst_ptrs)
+        if len(sp) != len(dp):
+            raise KvError("src and dst must have the same number of layers")
+        h = C.c_void_p()
+        _lib.check(_lib.lib().kvdp_plan_block_copy(C.byref(h), sp.ctypes.data, dp.ctypes.data, len(sp), prefix_dim,
+                                                   src_block_dim, dst_block_dim, suffix_dim, elem_size, device))
+        return cls(h, keepalive)
+
+    @classmethod
+    def contig(cls, layers: KvBlockStorage, contig: "KvContiguousBlocks", to_contig: bool,
+               device: int = -1) -> "CopyPlan":
+        """layer-separate <-> contiguous-per-block relayout."""
+        bd = layers.block_details
+        chunk = bd.bytes_per_token_block_per_layer() // 2
+        if contig.chunk_bytes != chunk or contig.num_layers != len(layers.layers):
+            raise KvError("contiguous slab geometry does not match the layer set")
+        lp = _u64(layers.layer_pointers())
+        h = C.c_void_p()
+        _lib.check(_lib.lib().kvdp_plan_contig(C.byref(h), lp.ctypes.data, len(lp), bd.layout.value,
+                                               layers.number_of_blocks(), chunk, C.c_void_p(contig.get_pointer()),
+                                               contig.number_of_blocks, int(to_contig), device))
+        return cls(h, (layers, contig))
+
+    @classmethod
+    def reshard(cls, src_layer_ptrs, dst_layer_ptrs_by_target, src_blocks: int, dst_blocks: int, block_size: int,
+                src_row_bytes: int, src_tp: int, dst_tp: int, src_rank: int, device: int = -1,
+                keepalive=None) -> "CopyPlan":
+        """TP reshard push (KvFirst caches). dst_layer_ptrs_by_target: [targets][layers] raw pointers
+        (local or peer-mapped)."""
+        sp = _u64(src_layer_ptrs)
+        dp = _u64(np.asarray(dst_layer_ptrs_by_target, dtype=np.uint64).reshape(-1))
+        h = C.c_void_p()
+        _lib.check(_lib.lib().kvdp_plan_reshard(C.byref(h), sp.ctypes.data, dp.ctypes.data, len(sp), src_blocks,
+                                                dst_blocks, block_size, src_row_bytes, src_tp, dst_tp, src_rank,
+                                                device))
+        return cls(h, keepalive)
+
+    @classmethod
+    def from_desc(cls, desc: "_lib.PlanDesc", keepalive=None) -> "CopyPlan":
+        h = C.c_void_p()
+        _lib.check(_lib.lib().kvdp_plan_create(C.byref(h), C.byref(desc)))
+        return cls(h, keepalive)
+
+
+class TransferEngine:
+    """Owner of a `kvdp_xfer*`: one stream + id staging; the v2 `CopyStream`."""
+
+    def __init__(self, max_pairs: int, device: int = -1):
+        _lib.require_gpu()
+        h = C.c_void_p()
+        _lib.check(_lib.lib().kvdp_xfer_create(C.byref(h), int(max_pairs), int(device)))
+        self._h = h
+
+    @property
+    def stream(self) -> int:
+        return int(_lib.lib().kvdp_xfer_stream(self._h) or 0)
+
+    def run(self, plan: CopyPlan, src_ids: Sequence[int], dst_ids: Sequence[int], layer_begin: int = 0,
+            layer_end: Optional[int] = None, check_dst_unique: bool = True, done_flag: int = 0,
+            done_value: int = 0, num_layers: Optional[int] = None) -> None:
+        if len(src_ids) != len(dst_ids):
+            raise KvError("src_block_ids and dst_block_ids must have the same length")
+        s, d = _ids32(src_ids), _ids32(dst_ids)
+        if layer_end is None:
+            if num_layers is None:
+                raise KvError("layer_end or num_layers is required")
+            layer_end = num_layers
+        flags = _lib.XFER_CHECK_DST_UNIQUE if check_dst_unique else 0
+        _lib.check(_lib.lib().kvdp_xfer_run(self._h, plan.handle, s.ctypes.data if len(s) else None,
+                                            d.ctypes.data if len(d) else None, len(s), int(layer_begin),
+                                            int(layer_end), flags, C.c_void_p(done_flag) if done_flag else None,
+                                            int(done_value)))
+
+    def signal(self, flag_ptr: int, value: int) -> None:
+        _lib.check(_lib.lib().kvdp_xfer_signal(self._h, C.c_void_p(flag_ptr), int(value)))
+
+    def sync(self) -> None:
+        _lib.check(_lib.lib().kvdp_xfer_sync(self._h))
+
+    def close(self) -> None:
+        if self._h is not None and self._h.value:
+            _lib.lib().kvdp_xfer_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class KvContiguousBlocks(Storage):
+    """Fully-contiguous-per-block slab `[block][layer][K|V][token][head][dim]` (not in the reference)."""
+
+    def __init__(self, number_of_blocks: int, num_layers: int, chunk_bytes: int, storage_type: StorageType):
+        self.number_of_blocks = int(number_of_blocks)
+        self.num_layers = int(num_layers)
+        self.chunk_bytes = int(chunk_bytes)
+        self.block_bytes = self.num_layers * 2 * self.chunk_bytes
+        nbytes = self.number_of_blocks * self.block_bytes
+        if storage_type.kind == "device":
+            self.storage: Storage = DeviceStorageOwned(nbytes, storage_type.device)
+        elif storage_type.kind == "pinned":
+            self.storage = CudaPinnedMemory(nbytes)
+        else:
+            raise KvError("System memory not yet supported")
+
+    def get_pointer(self) -> int:
+        return self.storage.get_pointer()
+
+    def storage_size(self) -> int:
+        return self.storage.storage_size()
+
+    def storage_type(self) -> StorageType:
+        return self.storage.storage_type()
+
+
+class HostTier:
+    """Offload/onboard between layer-separate HBM blocks and a pinned contiguous-per-block slab."""
+
+    def __init__(self, layers: KvBlockStorage, host: KvContiguousBlocks, staging_blocks: int = 32, device: int = -1):
+        if host.storage_type().kind != "pinned":
+            raise KvError("the host tier slab must be pinned memory")
+        bd = layers.block_details
+        chunk = bd.bytes_per_token_block_per_layer() // 2
+        if host.chunk_bytes != chunk or host.num_layers != len(layers.layers):
+            raise KvError("host slab geometry does not match the layer set")
+        lp = _u64(layers.layer_pointers())
+        h = C.c_void_p()
+        _lib.check(_lib.lib().kvdp_host_tier_create(C.byref(h), lp.ctypes.data, len(lp), bd.layout.value,
+                                                    layers.number_of_blocks(), chunk, C.c_void_p(host.get_pointer()),
+                                                    host.number_of_blocks, int(staging_blocks), device))
+        self._h = h
+        self._keep = (layers, host)
+
+    def offload(self, device_ids: Sequence[int], host_ids: Sequence[int]) -> None:
+        if len(device_ids) != len(host_ids):
+            raise KvError("device and host id lists must have the same length")
+        d, h = _ids32(device_ids), _ids32(host_ids)
+        _lib.check(_lib.lib().kvdp_host_tier_offload(self._h, d.ctypes.data, h.ctypes.data, len(d)))
+
+    def onboard(self, host_ids: Sequence[int], device_ids: Sequence[int]) -> None:
+        if len(device_ids) != len(host_ids):
+            raise KvError("device and host id lists must have the same length")
+        d, h = _ids32(device_ids), _ids32(host_ids)
+        _lib.check(_lib.lib().kvdp_host_tier_onboard(self._h, h.ctypes.data, d.ctypes.data, len(d)))
+
+    def sync(self) -> None:
+        _lib.check(_lib.lib().kvdp_host_tier_sync(self._h))
+
+    def close(self) -> None:
+        if self._h is not None and self._h.value:
+            _lib.lib().kvdp_host_tier_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# ---------------------------------------------------------------------------------------------- raw memory helpers
+def memcpy_sync(dst: int, src: int, nbytes: int) -> None:
+    _lib.check(_lib.lib().cuda_memcpy_sync(C.c_void_p(dst), C.c_void_p(src), int(nbytes)))
+
+
+def upload(dst_device_ptr: int, array: np.ndarray) -> None:
+    a = np.ascontiguousarray(array)
+    memcpy_sync(dst_device_ptr, a.ctypes.data, a.nbytes)
+
+
+def download(src_device_ptr: int, nbytes: int, dtype=np.uint8) -> np.ndarray:
+    out = np.empty(int(nbytes), dtype=np.uint8)
+    memcpy_sync(out.ctypes.data, src_device_ptr, nbytes)
+    return out.view(dtype)
