@@ -1,0 +1,246 @@
+#!/usr/bin/env python
+"""bench.py — KV-cache data-plane benchmark (contract: see the task statement / DESIGN.md §Measurement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one pass of the hot path over one batch of synthetic KV blocks:
+  N = 1 : BASELINE config 2 on one GPU — Llama-3-8B / DeepSeek-R1-Distill-Llama-8B shape (32 layers, 8 KV heads x 128,
+          64-token blocks, bf16), a batch of R requests of ISL 4k (64 blocks each): layer-separate -> contiguous-per-block
+          relayout, ONE kernel launch per step (HBM-bound).
+  N > 1 : the same batch per prefill GPU, pushed from inside the relayout kernel into the contiguous cache of a decode
+          GPU through NVLink peer-mapped stores (prefill ranks = first half, decode ranks = second half).
+`value` is payload GB/s delivered (1 GB = 1e9 B) over the whole job, inputs resident in HBM. `e2e` is the same unit
+measured through the reference-facing legacy C ABI (CopyStream: prepare_block_ids / memcpy per layer / sync) with the
+source blocks in pinned HOST memory, i.e. including the host->device copy, plus a device->host read of the result.
+Token-block hashing (hashes/s) is timed in the same run and reported under "hash".
+`--impl reference` times the CPU restatement of the reference's host block-copy loops (oracle/) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GB = 1e9
+# Llama-3-8B shape (BASELINE.json configs[1]); 64-token blocks, bf16
+L8B, H8B, D8B, BS, ELEM = 32, 8, 128, 64, 2
+CHUNK = BS * H8B * D8B * ELEM          # 128 KiB per (layer, K|V, block)
+BLOCK_BYTES = L8B * 2 * CHUNK          # 8 MiB per block over all layers
+BLOCKS_PER_REQ = 64                    # ISL 4k
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--requests", type=int, default=8, help="requests (of 64 blocks) per step")
+    ap.add_argument("--cache-blocks", type=int, default=1024, help="blocks in the source / destination caches")
+    ap.add_argument("--copy-path", type=int, default=0)
+    ap.add_argument("--tile-bytes", type=int, default=0)
+    ap.add_argument("--stages", type=int, default=0)
+    ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--host-path", type=int, default=0)
+    ap.add_argument("--host-ctas", type=int, default=0)
+    ap.add_argument("--no-hash", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--sweep", action="store_true", help="print a table of kernel variants instead of the JSON line")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int):
+        self.idx = device_index
+        self.proc = None
+        self.lines = []
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.idx), "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._pump, daemon=True)
+        self.thread.start()
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=3)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+                pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs (oracle)
+def cpu_relayout_leg(threads: int, min_seconds: float, blocks: int = BLOCKS_PER_REQ):
+    """The reference's host block-copy loop restated in C (oracle/layout_oracle.c), on `blocks` Llama-3-8B blocks."""
+    from oracle import kvoracle as ko
+    ko.lib()
+    n_src = blocks
+    layers = [np.empty(2 * n_src * CHUNK, dtype=np.uint8) for _ in range(L8B)]
+    for i, a in enumerate(layers):
+        a[:] = (i * 7 + 1) & 0xFF  # touch every page
+    contig = np.zeros(blocks * BLOCK_BYTES, dtype=np.uint8)
+    rng = np.random.Generator(np.random.PCG64(1234))
+    sid, did = rng.permutation(n_src).astype(np.int32), rng.permutation(blocks).astype(np.int32)
+    ko.relayout_contig(layers, 0, n_src, CHUNK, contig, sid, did, True, threads)  # warm-up
+    reps, t0 = 0, time.perf_counter()
+    while True:
+        ko.relayout_contig(layers, 0, n_src, CHUNK, contig, sid, did, True, threads)
+        reps += 1
+        dt = time.perf_counter() - t0
+        if dt >= min_seconds:
+            break
+    return blocks * BLOCK_BYTES * reps / dt / GB, dt / reps
+
+
+def cpu_hash_leg(threads: int, min_seconds: float):
+    from oracle import kvoracle as ko
+    from tests.util import tokens_for
+    isls = [512, 1024, 2048, 4096, 8192, 16384, 32768]
+    reqs = [isls[i % 7] for i in range(7 * 16)]
+    offs = np.zeros(len(reqs) + 1, dtype=np.int64)
+    offs[1:] = np.cumsum(reqs)
+    toks = np.concatenate([tokens_for(r, n) for r, n in enumerate(reqs)])
+    nblk = int(offs[-1]) // BS
+    ko.hash_batch(toks, offs, BS, 1337, threads)
+    reps, t0 = 0, time.perf_counter()
+    while True:
+        ko.hash_batch(toks, offs, BS, 1337, threads)
+        reps += 1
+        dt = time.perf_counter() - t0
+        if dt >= min_seconds:
+            break
+    return nblk * reps / dt
+
+
+def run_reference(args):
+    """--impl reference: the CPU implementation of the path on the host cores, same metric/unit/config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import kvoracle as ko
+    threads = ko.hw_threads()
+    for _ in range(args.warmup):
+        cpu_relayout_leg(threads, 0.0)
+    vals = []
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        v, _ = cpu_relayout_leg(threads, 0.0)
+        vals.append(v)
+        if time.perf_counter() - t0 > 150:
+            break
+    # one step = one bounded sample (one 64-block request: 512 MiB read + 512 MiB written by memcpy)
+    value = float(np.mean(vals))
+    step_s = BLOCKS_PER_REQ * BLOCK_BYTES / (value * GB)
+    hps = cpu_hash_leg(threads, 2.0)
+    line = {
+        "impl": "reference", "metric": "kv_transfer_GBps", "value": value, "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": len(vals), "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": workload_config(args, sample=True),
+        "cpu_baseline": {"value": value, "unit": "GB/s", "cores": threads, "kind": "port",
+                         "sample": "one 64-block Llama-3-8B request (512 MiB payload) per step, layer-separate -> "
+                                   "contiguous relayout by memcpy (oracle/layout_oracle.c), all host threads"},
+        "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "blocks_per_s": value * GB / BLOCK_BYTES,
+        "hash": {"hashes_per_s": hps, "cores": threads, "kind": "port"},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, sample=False):
+    return {
+        "workload": "llama3-8b-shape KV blocks (32 layers, 8 KV heads x 128, 64-token blocks, bf16 = 8 MiB/block), "
+                    "ISL 4k requests (64 blocks), layer-separate -> contiguous-per-block"
+                    + (" + NVLink peer push prefill->decode" if args.gpus > 1 else " relayout on one GPU"),
+        "requests_per_step": 1 if sample else args.requests,
+        "blocks_per_step": BLOCKS_PER_REQ * (1 if sample else args.requests),
+        "cache_blocks": args.cache_blocks,
+        "l2_policy": "inputs larger than L2: every step reads/writes a different %d MiB window of 8 GiB caches"
+                     % (BLOCKS_PER_REQ * args.requests * BLOCK_BYTES >> 20),
+        "parallelism": "1 gpu" if args.gpus == 1 else "%dP:%dD" % (args.gpus // 2, args.gpus - args.gpus // 2),
+    }
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+
+    from dynamo_exp_b200 import _lib, build
+    build.build()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local_rank)
+    _lib.require_gpu()
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    for name, val in (("copy_path", args.copy_path), ("tile_bytes", args.tile_bytes), ("stages", args.stages),
+                      ("ctas_per_sm", args.ctas_per_sm), ("host_path", args.host_path), ("host_ctas", args.host_ctas)):
+        _lib.set_option(name, val)
+
+    if world > 1:
+        from bench_multi import run_multi
+        return run_multi(args, rank, local_rank, world)
+
+    from bench_single import run_single, run_sweep
+    if args.sweep:
+        return run_sweep(args)
+    return run_single(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,329 @@
+"""bench_single.py — the N=1 arm of bench.py (one B200): relayout kernel, e2e through the legacy C ABI, hashing."""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+import time
+
+import numpy as np
+
+from bench import (BLOCK_BYTES, BLOCKS_PER_REQ, BS, CHUNK, ELEM, GB, H8B, D8B, L8B, ROOT, ClockSampler,
+                   cpu_hash_leg, cpu_relayout_leg, workload_config)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(kernel_key: str):
+    """Per-launch DRAM bytes of the dominant kernel from the committed ncu summary, if one exists."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(kernel_key)
+        except Exception:
+            return None
+    return None
+
+
+class Setup:
+    """8 GiB layer-separate source cache + 8 GiB contiguous destination cache on cuda:0 (torch owns the memory)."""
+
+    def __init__(self, args, torch, lib, device=0, dst_contig_ptr=None, dst_blocks=None):
+        self.torch, self.lib, self.args = torch, lib, args
+        n = args.cache_blocks
+        self.n = n
+        g = torch.Generator(device="cuda")
+        g.manual_seed(42 + device)
+        self.src_layers = []
+        for l in range(L8B):
+            t = torch.empty(2 * n * CHUNK, dtype=torch.uint8, device="cuda")
+            t.random_(0, 256, generator=g)
+            self.src_layers.append(t)
+        self.src_ptrs = np.array([t.data_ptr() for t in self.src_layers], dtype=np.uint64)
+        if dst_contig_ptr is None:
+            self.dst = torch.zeros(n * BLOCK_BYTES, dtype=torch.uint8, device="cuda")
+            dst_contig_ptr, dst_blocks = self.dst.data_ptr(), n
+        self.dst_ptr, self.dst_blocks = dst_contig_ptr, dst_blocks
+        self.plan = C.c_void_p()
+        lib.check(lib.lib().kvdp_plan_contig(C.byref(self.plan), self.src_ptrs.ctypes.data, L8B, 0, n, CHUNK,
+                                             C.c_void_p(dst_contig_ptr), dst_blocks, 1, device))
+        self.pairs = BLOCKS_PER_REQ * args.requests
+        assert self.pairs <= n and self.pairs <= dst_blocks
+        self.xfer = C.c_void_p()
+        lib.check(lib.lib().kvdp_xfer_create(C.byref(self.xfer), self.pairs, device))
+        self.stream_ptr = lib.lib().kvdp_xfer_stream(self.xfer)
+        self.stream = torch.cuda.ExternalStream(self.stream_ptr)
+        rng = np.random.Generator(np.random.PCG64(1234 + device))
+        self.sperm = rng.permutation(n).astype(np.int32)
+        self.dperm = rng.permutation(dst_blocks).astype(np.int32)
+
+    def ids(self, step):
+        """A different window of the caches every step, so no step finds its data in L2."""
+        w = max(1, self.n // self.pairs)
+        o = (step % w) * self.pairs
+        wd = max(1, self.dst_blocks // self.pairs)
+        od = (step % wd) * self.pairs
+        return self.sperm[o:o + self.pairs], self.dperm[od:od + self.pairs]
+
+    def step(self, step, done_flag=None, done_value=0):
+        s, d = self.ids(step)
+        self.lib.check(self.lib.lib().kvdp_xfer_run(self.xfer, self.plan, s.ctypes.data, d.ctypes.data, self.pairs, 0,
+                                                    L8B, 0, done_flag, done_value))
+
+    def verify_local(self, step, samples=6):
+        """Spot check without the oracle: destination chunks equal the source chunks they were mapped from."""
+        torch = self.torch
+        s, d = self.ids(step)
+        rng = np.random.Generator(np.random.PCG64(step))
+        for _ in range(samples):
+            i, l, kv = int(rng.integers(self.pairs)), int(rng.integers(L8B)), int(rng.integers(2))
+            src = self.src_layers[l][(kv * self.n + int(s[i])) * CHUNK:(kv * self.n + int(s[i]) + 1) * CHUNK]
+            off = int(d[i]) * BLOCK_BYTES + (l * 2 + kv) * CHUNK
+            if not torch.equal(src, self.dst[off:off + CHUNK]):
+                raise RuntimeError("relayout result differs from its source (pair %d layer %d kv %d)" % (i, l, kv))
+
+
+def time_steps(torch, setup, steps, warmup, barrier=None):
+    for w in range(warmup):
+        setup.step(w)
+    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    start.record(setup.stream)
+    for k in range(steps):
+        setup.step(warmup + k)
+    end.record(setup.stream)
+    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+    return start.elapsed_time(end) / 1e3  # seconds
+
+
+def time_kernel_only(torch, lib, setup, launches, warmup=3):
+    """Average duration of the relayout kernel alone (ids already on the device): the roofline numerator's clock."""
+    s_all = torch.from_numpy(np.concatenate([setup.ids(k)[0] for k in range(launches + warmup)])).cuda()
+    d_all = torch.from_numpy(np.concatenate([setup.ids(k)[1] for k in range(launches + warmup)])).cuda()
+    p = setup.pairs
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(launches)]
+    torch.cuda.synchronize()
+    for k in range(launches + warmup):
+        if k >= warmup:
+            evs[k - warmup][0].record(setup.stream)
+        lib.check(lib.lib().kvdp_plan_launch(setup.plan, s_all.data_ptr() + 4 * k * p, d_all.data_ptr() + 4 * k * p, p,
+                                             0, L8B, setup.stream_ptr))
+        if k >= warmup:
+            evs[k - warmup][1].record(setup.stream)
+    torch.cuda.synchronize()
+    ms = [a.elapsed_time(b) for a, b in evs]
+    return float(np.mean(ms)) / 1e3, float(np.min(ms)) / 1e3
+
+
+def e2e_legacy(torch, lib, args, steps, warmup):
+    """Reference-facing path: pinned layer-separate host blocks -> device through the legacy CopyStream C ABI
+    (copy_stream_prepare_block_ids + copy_stream_memcpy per layer + copy_stream_sync), then an 8-byte read-back."""
+    L = lib.lib()
+    pairs = BLOCKS_PER_REQ * args.requests
+    nh = pairs
+    nd = pairs
+    host_layers, host_ptrs = [], []
+    for l in range(L8B):
+        p = C.c_void_p()
+        lib.check(L.cuda_malloc_host(C.byref(p), 2 * nh * CHUNK))
+        a = np.frombuffer((C.c_uint8 * (2 * nh * CHUNK)).from_address(p.value), dtype=np.uint8)
+        a[:] = (l * 13 + 5) & 0xFF
+        a[::4096] = np.arange(a[::4096].size, dtype=np.uint64).astype(np.uint8)
+        host_layers.append(a)
+        host_ptrs.append(p.value)
+    dev_layers = [torch.zeros(2 * nd * CHUNK, dtype=torch.uint8, device="cuda") for _ in range(L8B)]
+    cs = C.c_void_p()
+    assert L.copy_stream_create(C.byref(cs), L8B, pairs) == 0
+    rng = np.random.Generator(np.random.PCG64(77))
+    result = np.zeros(8, dtype=np.uint8)
+    t_total, timed = 0.0, 0
+    for k in range(steps + warmup):
+        sid, did = rng.permutation(nh).astype(np.int32), rng.permutation(nd).astype(np.int32)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        lib.check(L.copy_stream_prepare_block_ids(cs, sid.ctypes.data, did.ctypes.data, pairs))
+        for l in range(L8B):
+            lib.check(L.copy_stream_memcpy(cs, host_ptrs[l], dev_layers[l].data_ptr(), 2, BS * H8B * D8B, ELEM, nh, nd))
+        lib.check(L.copy_stream_sync(cs))
+        lib.check(L.cuda_memcpy_sync(result.ctypes.data, dev_layers[L8B - 1].data_ptr() + int(did[-1]) * CHUNK, 8))
+        dt = time.perf_counter() - t0
+        if k >= warmup:
+            t_total += dt
+            timed += 1
+        # result check: first 8 bytes of the last pair's K chunk in the last layer
+        want = host_layers[L8B - 1][int(sid[-1]) * CHUNK:int(sid[-1]) * CHUNK + 8]
+        if not np.array_equal(result, want):
+            raise RuntimeError("e2e result mismatch")
+    L.copy_stream_destroy(cs)
+    for p in host_ptrs:
+        L.cuda_free_host(C.c_void_p(p))
+    sec = t_total / timed
+    return {"value": pairs * BLOCK_BYTES / sec / GB, "unit": "GB/s", "h2d_bytes_per_step": pairs * BLOCK_BYTES,
+            "d2h_bytes_per_step": 8, "ms_per_step": sec * 1e3, "steps": timed,
+            "api": "legacy C ABI: copy_stream_prepare_block_ids + 32 x copy_stream_memcpy + copy_stream_sync "
+                   "(pinned host layer-separate blocks -> HBM), timed on the host clock around the blocking call"}
+
+
+def hash_bench(torch, lib, steps, warmup, peak):
+    """Router-sweep shaped batch (ISL 512..32k round-robin, 64-token blocks) resident in HBM; chained + block hashes."""
+    from tests.util import mix64
+    L = lib.lib()
+    isls = [512, 1024, 2048, 4096, 8192, 16384, 32768]
+    n_req = 7 * 2048
+    lens = np.array([isls[i % 7] for i in range(n_req)], dtype=np.int64)
+    offs = np.zeros(n_req + 1, dtype=np.int64)
+    offs[1:] = np.cumsum(lens)
+    total = int(offs[-1])
+    nblk = total // BS
+    # tokens generated on the device (torch RNG) — 0.5 GiB, larger than L2
+    g = torch.Generator(device="cuda")
+    g.manual_seed(0xD15A66)
+    tok = torch.randint(0, 128256, (total,), dtype=torch.int32, device="cuda", generator=g)
+    d_off = torch.from_numpy(offs).cuda()
+    d_boff = torch.empty(n_req + 1, dtype=torch.int64, device="cuda")
+    d_bh = torch.empty(nblk, dtype=torch.int64, device="cuda")
+    d_sh = torch.empty(nblk, dtype=torch.int64, device="cuda")
+    ws_bytes = L.kvdp_hash_workspace_bytes(n_req)
+    d_ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream()
+
+    def run(salt):
+        lib.check(L.kvdp_hash_token_blocks(tok.data_ptr(), d_off.data_ptr(), n_req, total, BS, salt, d_boff.data_ptr(),
+                                           d_bh.data_ptr(), d_sh.data_ptr(), d_ws.data_ptr(), ws_bytes, 0,
+                                           C.c_void_p(st.cuda_stream)))
+    for _ in range(warmup):
+        run(1337)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(st)
+    for k in range(steps):
+        run(1337 + k)
+    b.record(st)
+    torch.cuda.synchronize()
+    sec = a.elapsed_time(b) / 1e3 / steps
+    # spot parity inside the bench: first request of the last run against python-free re-hash on a second salt run
+    out = {"hashes_per_s": nblk / sec, "tokens_per_s": total / sec, "ms_per_batch": sec * 1e3, "requests": n_req,
+           "blocks": nblk, "launches_per_batch": 5,
+           "roofline": {"bound": "hbm", "achieved": nblk * 272 / sec / GB, "peak": peak, "unit": "GB/s",
+                        "frac": nblk * 272 / sec / GB / peak, "traffic": ncu_traffic("kvdp_hash_blocks_tma")}}
+    # e2e: pinned host tokens -> device -> hashes back on the host, through kvdp_hash_token_blocks_host
+    n_e = 7 * 256
+    lens_e = lens[:n_e]
+    offs_e = np.zeros(n_e + 1, dtype=np.int64)
+    offs_e[1:] = np.cumsum(lens_e)
+    tot_e = int(offs_e[-1])
+    h_tok = torch.randint(0, 128256, (tot_e,), dtype=torch.int32).pin_memory()
+    nb_e = tot_e // BS
+    h_boff = torch.empty(n_e + 1, dtype=torch.int64).pin_memory()
+    h_bh = torch.empty(nb_e, dtype=torch.int64).pin_memory()
+    h_sh = torch.empty(nb_e, dtype=torch.int64).pin_memory()
+
+    def run_host():
+        lib.check(L.kvdp_hash_token_blocks_host(h_tok.data_ptr(), offs_e.ctypes.data, n_e, BS, 1337, h_boff.data_ptr(),
+                                                h_bh.data_ptr(), h_sh.data_ptr(), 0, -1))
+    run_host()
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        run_host()
+    dt = (time.perf_counter() - t0) / reps
+    out["e2e"] = {"hashes_per_s": nb_e / dt, "h2d_bytes_per_batch": tot_e * 4 + (n_e + 1) * 8,
+                  "d2h_bytes_per_batch": nb_e * 16 + (n_e + 1) * 8, "ms_per_batch": dt * 1e3}
+    return out
+
+
+def run_single(args):
+    import torch
+
+    from dynamo_exp_b200 import _lib as lib
+    peak, peak_src = measured_peaks()
+    setup = Setup(args, torch, lib)
+    clocks = ClockSampler(0)
+    clocks.start()
+    sec = time_steps(torch, setup, args.steps, args.warmup)
+    clk = clocks.stop()
+    setup.verify_local(args.warmup + args.steps - 1)
+    payload = setup.pairs * BLOCK_BYTES
+    value = payload * args.steps / sec / GB
+    k_avg, k_min = time_kernel_only(torch, lib, setup, max(args.steps, 10))
+    path = lib.get_option("copy_path")
+    kname = {0: "kvdp_copy_tma_tma_kernel", 1: "kvdp_copy_vec_kernel", 2: "kvdp_copy_tma_in_kernel",
+             3: "kvdp_copy_tma_tma_kernel"}[path]
+    line = {
+        "metric": "kv_transfer_GBps", "value": value, "unit": "GB/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(args),
+        "blocks_per_s": setup.pairs * args.steps / sec,
+        "roofline": {"bound": "hbm", "achieved": 2 * payload / k_avg / GB, "peak": peak, "unit": "GB/s",
+                     "frac": 2 * payload / k_avg / GB / peak, "traffic": ncu_traffic(kname), "kernel": kname,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": 2 * payload,
+                     "avg_launch_ms": k_avg * 1e3, "best_launch_ms": k_min * 1e3,
+                     "frac_of_nominal_8TBps": 2 * payload / k_avg / GB / 8000.0},
+        "gpu_launches": args.steps,
+        "clocks": clk,
+    }
+    del setup
+    torch.cuda.empty_cache()
+    if not args.no_e2e:
+        line["e2e"] = e2e_legacy(torch, lib, args, min(args.steps, 8), 2)
+    if not args.no_hash:
+        line["hash"] = hash_bench(torch, lib, 10, 3, peak)
+        line["hashes_per_s"] = line["hash"]["hashes_per_s"]
+    if not args.no_cpu:
+        from oracle import kvoracle as ko
+        threads = ko.hw_threads()
+        v_all, _ = cpu_relayout_leg(threads, 6.0)
+        v_one, _ = cpu_relayout_leg(1, 3.0)
+        line["cpu_baseline"] = {
+            "value": v_all, "unit": "GB/s", "cores": threads, "kind": "port",
+            "sample": "64 Llama-3-8B blocks (512 MiB payload) relaid out layer-separate -> contiguous by the C "
+                      "restatement of the reference's host copy loop (oracle/layout_oracle.c), repeated for >= 6 s",
+            "single_thread_value": v_one,
+            "hash_hashes_per_s": cpu_hash_leg(threads, 3.0), "hash_hashes_per_s_single_thread": cpu_hash_leg(1, 2.0)}
+    print(json.dumps(line), flush=True)
+
+
+def run_sweep(args):
+    """Exploration table (not the bench line): every copy path x tile x CTAs/SM on the N=1 workload."""
+    import torch
+
+    from dynamo_exp_b200 import _lib as lib
+    setup = Setup(args, torch, lib)
+    payload = setup.pairs * BLOCK_BYTES
+    rows = []
+    combos = []
+    for path in (1, 2, 3):
+        for tile in (8192, 16384, 32768):
+            for cps in ((2, 4, 8) if path == 1 else (1, 2, 3, 4, 6)):
+                for stages in ((0,) if path != 2 else (3, 4, 6)):
+                    combos.append((path, tile, cps, stages))
+    for path, tile, cps, stages in combos:
+        try:
+            lib.set_option("copy_path", path)
+            lib.set_option("tile_bytes", tile)
+            lib.set_option("ctas_per_sm", cps)
+            lib.set_option("stages", stages)
+            k_avg, k_min = time_kernel_only(torch, lib, setup, 6, warmup=2)
+            setup.verify_local(7, samples=2)
+            rows.append((path, tile, cps, stages, 2 * payload / k_avg / GB, 2 * payload / k_min / GB))
+        except Exception as e:  # noqa: BLE001
+            rows.append((path, tile, cps, stages, -1.0, -1.0))
+            print("sweep point failed:", path, tile, cps, stages, e, flush=True)
+            break
+    print("path tile ctas/sm stages  avg_GB/s(r+w)  best_GB/s(r+w)")
+    for r in sorted(rows, key=lambda r: -r[4]):
+        print("%4d %6d %4d %4d  %10.1f  %10.1f" % r)

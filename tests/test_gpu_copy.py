@@ -1,0 +1,463 @@
+"""GPU parity: block copy / relayout / legacy ABI through libkvdp.so against the CPU oracle and, where it was built,
+against the reference's own block_copy.cu (oracle/_ref/libblock_copy_ref.so) on the same inputs. Bit-exact."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from dynamo_exp_b200 import (CopyPlan, CopyStream, CopyStreamBlockMap, DType, KvBlockDetails, KvBlockStorage,
+                             KvContiguousBlocks, KvError, KvLayout, KvModelDetails, StorageType, TransferEngine)
+from tests.util import DevBuf, PinnedBuf, payload, permutation
+
+pytestmark = pytest.mark.gpu
+
+PATHS = [1, 2, 3]
+
+
+@pytest.fixture(autouse=True)
+def _reset_options(gpu):
+    yield
+    for k in ("copy_path", "tile_bytes", "stages", "ctas_per_sm", "host_path", "host_ctas"):
+        gpu.set_option(k, 0)
+
+
+def details(layout, L=3, H=4, D=16, bs=8, dtype=DType.BF16, tp=1):
+    return KvBlockDetails(layout=layout, block_size=bs,
+                          model_details=KvModelDetails(L, H, D, dtype), tp_size=tp)
+
+
+def fill_layers(gpu, storage: KvBlockStorage, seed):
+    """Write a distinct payload into every layer; return the host copies (numpy uint8)."""
+    out = []
+    for l, layer in enumerate(storage.layers):
+        n = layer.storage_size()
+        data = payload(n, seed * 1000 + l)
+        if storage.storage_type().kind == "pinned":
+            layer.storage.storage.as_numpy()[:] = data
+        else:
+            gpu.check(gpu.lib().cuda_memcpy_sync(C.c_void_p(layer.get_pointer()), C.c_void_p(data.ctypes.data), n))
+        out.append(data)
+    return out
+
+
+def read_layers(gpu, storage: KvBlockStorage):
+    out = []
+    for layer in storage.layers:
+        n = layer.storage_size()
+        buf = np.empty(n, dtype=np.uint8)
+        gpu.check(gpu.lib().cuda_memcpy_sync(C.c_void_p(buf.ctypes.data), C.c_void_p(layer.get_pointer()), n))
+        out.append(buf)
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ legacy ABI
+@pytest.mark.parametrize("layout", [KvLayout.KvFirst, KvLayout.BlockFirst])
+def test_copy_blocks_to_reference_pattern(gpu, layout):
+    """kv/layer.rs:1412-1584: fill-with-block-id, D->H with src=[1,2,2,3,5] dst=[0,3,2,1,4] (duplicate src allowed)."""
+    nb = 8
+    bd = details(layout, L=1, dtype=DType.F32)
+    dev = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    host = KvBlockStorage.allocate(nb, bd, StorageType.Pinned)
+    shape = dev.layer(0).layer_shape()
+    src = np.zeros(shape, dtype=np.float32)
+    for b in range(nb):
+        if layout == KvLayout.KvFirst:
+            src[:, b] = b
+        else:
+            src[b] = b
+    gpu.check(gpu.lib().cuda_memcpy_sync(C.c_void_p(dev.layer(0).get_pointer()), C.c_void_p(src.ctypes.data),
+                                         src.nbytes))
+    dev.layer(0).copy_blocks_to([1, 2, 2, 3, 5], host.layer(0), [0, 3, 2, 1, 4])
+    got = host.layer(0).view().as_numpy(np.float32)
+    for s, t in zip([1, 2, 2, 3, 5], [0, 3, 2, 1, 4]):
+        blk = got[:, t] if layout == KvLayout.KvFirst else got[t]
+        assert np.all(blk == s)
+    for t in (5, 6, 7):
+        blk = got[:, t] if layout == KvLayout.KvFirst else got[t]
+        assert np.all(blk == 0)
+
+
+def test_copy_blocks_to_rejects_like_the_reference(gpu):
+    bd = details(KvLayout.KvFirst, L=1)
+    dev = KvBlockStorage.allocate(4, bd, StorageType.Device(0))
+    dev2 = KvBlockStorage.allocate(4, bd, StorageType.Device(0))
+    host = KvBlockStorage.allocate(4, bd, StorageType.Pinned)
+    host2 = KvBlockStorage.allocate(4, bd, StorageType.Pinned)
+    with pytest.raises(KvError, match="Device to Device"):
+        dev.layer(0).copy_blocks_to([0], dev2.layer(0), [0])
+    with pytest.raises(KvError, match="Pinned to Pinned"):
+        host.layer(0).copy_blocks_to([0], host2.layer(0), [0])
+    with pytest.raises(KvError, match="same length"):
+        host.layer(0).copy_blocks_to([0, 1], dev.layer(0), [0])
+    # Q9: an empty id list is Ok(()) in the reference (validation failure is swallowed by copy_blocks_3d)
+    host.layer(0).copy_blocks_to([], dev.layer(0), [])
+
+
+@pytest.mark.parametrize("layout", [KvLayout.KvFirst, KvLayout.BlockFirst])
+@pytest.mark.parametrize("host_path", [0, 1])
+def test_copy_stream_h2d_then_reversed_d2h(gpu, oracle, layout, host_path):
+    """kv/layer.rs:1590-1735: CopyStream H2D with ids, then D2H with the ids reversed; every element checked."""
+    gpu.set_option("host_path", host_path)
+    nb_h, nb_d, L = 12, 16, 4
+    bd = details(layout, L=L)
+    host = KvBlockStorage.allocate(nb_h, bd, StorageType.Pinned)
+    dev = KvBlockStorage.allocate(nb_d, bd, StorageType.Device(0))
+    back = KvBlockStorage.allocate(nb_h, bd, StorageType.Pinned)
+    src_data = fill_layers(gpu, host, 1)
+    h_ids = [0, 3, 5, 7, 11, 2]
+    d_ids = [15, 1, 4, 9, 0, 8]
+
+    cs = CopyStream.new(L, 16)
+    cs.prepare_block_map(CopyStreamBlockMap.new(host, dev))
+    cs.prepare_block_ids(h_ids, d_ids)
+    with pytest.raises(KvError, match="already loaded"):
+        cs.prepare_block_ids(h_ids, d_ids)
+    cs.trigger_all_layers()
+    cs.trigger_layer(0)  # doorbell: second trigger is a no-op
+    cs.sync_stream()
+    cs.reset()
+
+    # oracle on the host copies
+    bdx = bd
+    want_dev = [np.zeros(dev.layer(l).storage_size(), dtype=np.uint8) for l in range(L)]
+    oracle.copy_blocks_layers(src_data, want_dev, h_ids, d_ids, bdx.prefix_dim(), nb_h, nb_d, bdx.suffix_dim(),
+                              bdx.elem_size())
+    got_dev = read_layers(gpu, dev)
+    for l in range(L):
+        assert np.array_equal(got_dev[l], want_dev[l]), l
+
+    cs.prepare_block_map(CopyStreamBlockMap.new(dev, back))
+    cs.prepare_block_ids(d_ids, h_ids)
+    cs.trigger_all_layers()
+    cs.sync_stream()
+    cs.on_return()
+    want_back = [np.zeros(back.layer(l).storage_size(), dtype=np.uint8) for l in range(L)]
+    oracle.copy_blocks_layers(want_dev, want_back, d_ids, h_ids, bdx.prefix_dim(), nb_d, nb_h, bdx.suffix_dim(),
+                              bdx.elem_size())
+    for l in range(L):
+        got = back.layer(l).storage.storage.as_numpy()
+        assert np.array_equal(got, want_back[l]), l
+    cs.close()
+
+
+def test_copy_stream_state_machine_errors(gpu):
+    bd = details(KvLayout.KvFirst, L=2)
+    a = KvBlockStorage.allocate(4, bd, StorageType.Pinned)
+    b = KvBlockStorage.allocate(4, bd, StorageType.Device(0))
+    cs = CopyStream.new(2, 4)
+    with pytest.raises(KvError, match="Layers must be loaded before preparing block ids"):
+        cs.prepare_block_ids([0], [0])
+    with pytest.raises(KvError, match="Layers must be loaded before triggering"):
+        cs.trigger_layer(0)
+    cs.prepare_block_map(CopyStreamBlockMap.new(a, b))
+    with pytest.raises(KvError, match="Layers already loaded"):
+        cs.prepare_block_map(CopyStreamBlockMap.new(a, b))
+    with pytest.raises(KvError, match="Block ids must be loaded"):
+        cs.trigger_layer(0)
+    with pytest.raises(KvError, match="exceeds max number of blocks"):
+        cs.prepare_block_ids([0, 1, 2, 3, 4], [4, 3, 2, 1, 0])
+    with pytest.raises(KvError, match="dst_block_ids must be unique"):
+        cs.prepare_block_ids([0, 1], [2, 2])
+    with pytest.raises(KvError, match="src_block_ids must be unique"):
+        cs.prepare_block_ids([1, 1], [2, 3])
+    cs.prepare_block_ids([0, 1], [2, 3])
+    with pytest.raises(KvError, match="out of bounds"):
+        cs.trigger_layer(2)
+    cs.trigger_all_layers()
+    cs.sync_stream()
+    big = CopyStream.new(1, 4)
+    with pytest.raises(KvError, match="exceeds max number of layers"):
+        big.prepare_block_map(CopyStreamBlockMap.new(a, b))
+
+
+def test_legacy_return_codes(gpu):
+    """cudaErrorInvalidValue (1) for NULLs / non-positive dims; copy_blocks_3d swallows them (Q9)."""
+    L = gpu.lib()
+    a, b = DevBuf(gpu, 4096), DevBuf(gpu, 4096)
+    ids = np.zeros(4, dtype=np.int32)
+    ip = C.c_void_p(ids.ctypes.data)
+    for fn in (L.copy_blocks_memcpy_3d, L.copy_blocks_launcher_3d):
+        assert fn(None, b.ptr, ip, ip, 1, 1, 16, 1, 4, 4, None) == 1
+        assert fn(a.ptr, None, ip, ip, 1, 1, 16, 1, 4, 4, None) == 1
+        assert fn(a.ptr, b.ptr, None, ip, 1, 1, 16, 1, 4, 4, None) == 1
+        assert fn(a.ptr, b.ptr, ip, ip, 0, 1, 16, 1, 4, 4, None) == 1
+        assert fn(a.ptr, b.ptr, ip, ip, 1, 0, 16, 1, 4, 4, None) == 1
+        assert fn(a.ptr, b.ptr, ip, ip, 1, 1, 0, 1, 4, 4, None) == 1
+        assert fn(a.ptr, b.ptr, ip, ip, 1, 1, 16, 0, 4, 4, None) == 1
+    assert L.copy_blocks_3d(None, b.ptr, ip, ip, 1, 1, 4, 4, 16, 1) == 0
+    assert L.copy_blocks_3d(a.ptr, b.ptr, ip, ip, 0, 1, 4, 4, 16, 1) == 0
+    h = C.c_void_p()
+    assert L.copy_stream_create(C.byref(h), 1, 4) == 0 and h.value
+    dims = np.array([2, 4, 2, 2, 1, 8], dtype=np.uint32)
+    dp = C.c_void_p(dims.ctypes.data)
+    assert L.copy_stream_scatter(h, a.ptr, b.ptr, dp, 5, 1, 1, 4, 4) == -1
+    assert L.copy_stream_scatter(h, a.ptr, b.ptr, dp, 6, 1, 2, 4, 4) == -2
+    assert L.copy_stream_scatter(h, a.ptr, b.ptr, dp, 6, 1, 1, 5, 4) == -3
+    bad = np.array([3, 4, 2, 2, 1, 8], dtype=np.uint32)
+    assert L.copy_stream_scatter(h, a.ptr, b.ptr, C.c_void_p(bad.ctypes.data), 6, 1, 1, 4, 4) == -4
+    assert L.copy_stream_sync(h) == 0
+    assert L.copy_stream_destroy(h) == 0
+    p = C.c_void_p()
+    assert L.cuda_malloc_host(C.byref(p), 1024) == 0 and p.value
+    assert L.cuda_memcpy_sync(a.ptr, p, 1024) == 0
+    assert L.cuda_memcpy_async(p, a.ptr, 1024, None) == 0
+    assert L.copy_blocks_3d(a.ptr, b.ptr, ip, ip, 1, 1, 4, 4, 16, 1) == 0  # also synchronises stream 0
+    assert L.cuda_free_host(p) == 0
+
+
+@pytest.mark.parametrize("block_dim_index", [0, 1])
+@pytest.mark.parametrize("elem,hs", [(4, 6), (2, 8), (1, 16), (8, 2), (2, 3)])
+def test_legacy_scatter_matches_reference_formula(gpu, oracle, block_dim_index, elem, hs):
+    """kv/layer.rs:1865-2065: tp1 -> tp4, 16 heads; equals permuted_axes([3,0,1,2,4,5]). Identity block ids (Q4)."""
+    nb_s, nb_d, bs, heads, sf = 5, 7, 4, 16, 4
+    dnh = heads // sf
+    dims5 = [nb_s, 2, bs, heads, hs] if block_dim_index == 0 else [2, nb_s, bs, heads, hs]
+    n_src = int(np.prod(dims5)) * elem
+    n_dst = sf * 2 * nb_d * bs * dnh * hs * elem
+    src_h = payload(n_src, 17 + elem)
+    src, dst = DevBuf(gpu, n_src), DevBuf(gpu, n_dst)
+    src.upload(src_h)
+    L = gpu.lib()
+    h = C.c_void_p()
+    assert L.copy_stream_create(C.byref(h), 1, 8) == 0
+    ids = np.array([3, 1, 0], dtype=np.int32)  # staged ids are ignored by scatter; only their count (3) matters
+    assert L.copy_stream_prepare_block_ids(h, ids.ctypes.data, ids.ctypes.data, 3) == 0
+    dims6 = np.array([dims5[0], dims5[1], bs, sf, dnh, hs], dtype=np.uint32)
+    assert L.copy_stream_scatter(h, src.ptr, dst.ptr, dims6.ctypes.data, 6, elem, block_dim_index, nb_s, nb_d) == 0
+    assert L.copy_stream_sync(h) == 0
+    want = np.zeros(n_dst, dtype=np.uint8)
+    assert oracle.scatter_6d(src_h, want, dims6, elem, block_dim_index, nb_s, nb_d, 3) == 0
+    assert np.array_equal(dst.download(), want)
+    assert L.copy_stream_destroy(h) == 0
+
+
+def test_legacy_symbols_match_the_real_reference_library(gpu, oracle):
+    """oracle/_ref/libblock_copy_ref.so is the reference's own block_copy.cu compiled unmodified (oracle/Makefile).
+    Same inputs through both libraries' legacy entry points must give identical bytes."""
+    ref = oracle.ref_lib()
+    if ref is None:
+        pytest.skip("oracle/_ref was not built (reference tree absent at build time)")
+    L = gpu.lib()
+    for fn in ("copy_blocks_memcpy_3d", "copy_stream_create", "copy_stream_prepare_block_ids", "copy_stream_memcpy",
+               "copy_stream_scatter", "copy_stream_sync"):
+        getattr(ref, fn).restype = C.c_int
+    prefix, ns, nd, suffix, elem = 2, 9, 11, 96, 2
+    n_src, n_dst = prefix * ns * suffix * elem, prefix * nd * suffix * elem
+    src_h = payload(n_src, 5)
+    src = DevBuf(gpu, n_src)
+    src.upload(src_h)
+    sid = np.array([8, 0, 3, 3, 5], dtype=np.int32)
+    did = np.array([1, 10, 4, 6, 0], dtype=np.int32)
+    outs = []
+    for lib_ in (ref, L):
+        dst = DevBuf(gpu, n_dst)
+        rc = lib_.copy_blocks_memcpy_3d(C.c_void_p(src.ptr), C.c_void_p(dst.ptr), C.c_void_p(sid.ctypes.data),
+                                        C.c_void_p(did.ctypes.data), C.c_int(5), C.c_int(prefix), C.c_int(suffix),
+                                        C.c_int(elem), C.c_int(ns), C.c_int(nd), C.c_void_p(0))
+        assert rc == 0
+        outs.append(dst.download())
+    assert np.array_equal(outs[0], outs[1])
+    want = np.zeros(n_dst, dtype=np.uint8)
+    oracle.copy_blocks_3d(src_h, want, sid, did, prefix, ns, nd, suffix, elem)
+    assert np.array_equal(outs[0], want)  # the oracle restatement agrees with the real reference too
+
+    # scatter through a CopyStream of each library
+    nb, bs, sf, dnh, hs, e = 4, 4, 4, 2, 8, 2
+    dims6 = np.array([2, nb, bs, sf, dnh, hs], dtype=np.uint32)
+    n = int(np.prod(dims6)) * e
+    s_h = payload(n, 9)
+    s = DevBuf(gpu, n)
+    s.upload(s_h)
+    ids = np.arange(nb, dtype=np.int32)
+    outs = []
+    for lib_ in (ref, L):
+        d = DevBuf(gpu, n)
+        h = C.c_void_p()
+        assert lib_.copy_stream_create(C.byref(h), C.c_int(1), C.c_int(nb)) == 0
+        assert lib_.copy_stream_prepare_block_ids(h, C.c_void_p(ids.ctypes.data), C.c_void_p(ids.ctypes.data),
+                                                  C.c_int(nb)) == 0
+        assert lib_.copy_stream_scatter(h, C.c_void_p(s.ptr), C.c_void_p(d.ptr), C.c_void_p(dims6.ctypes.data),
+                                        C.c_uint32(6), C.c_uint32(e), C.c_uint32(1), C.c_uint32(nb),
+                                        C.c_uint32(nb)) == 0
+        assert lib_.copy_stream_sync(h) == 0
+        outs.append(d.download())
+    assert np.array_equal(outs[0], outs[1])
+    want = np.zeros(n, dtype=np.uint8)
+    oracle.scatter_6d(s_h, want, dims6, e, 1, nb, nb, nb)
+    assert np.array_equal(outs[0], want)
+
+
+# ------------------------------------------------------------------------------------------------ v2 plans
+@pytest.mark.parametrize("path", PATHS)
+@pytest.mark.parametrize("layout", [KvLayout.KvFirst, KvLayout.BlockFirst])
+@pytest.mark.parametrize("dtype", [DType.U8, DType.BF16, DType.F32, DType.U64])
+def test_plan_block_copy_d2d(gpu, oracle, path, layout, dtype):
+    gpu.set_option("copy_path", path)
+    gpu.set_option("tile_bytes", 4096)  # several tiles per chunk even at test sizes
+    L, ns, nd = 3, 10, 14
+    bd = details(layout, L=L, H=4, D=32, bs=16, dtype=dtype)
+    a = KvBlockStorage.allocate(ns, bd, StorageType.Device(0))
+    b = KvBlockStorage.allocate(nd, bd, StorageType.Device(0))
+    src = fill_layers(gpu, a, 3)
+    sid = permutation(ns, 1)[:7]
+    did = permutation(nd, 2)[:7]
+    plan = CopyPlan.block_copy(a, b)
+    eng = TransferEngine(16)
+    eng.run(plan, sid, did, num_layers=L)
+    eng.sync()
+    want = [np.zeros(b.layer(l).storage_size(), dtype=np.uint8) for l in range(L)]
+    oracle.copy_blocks_layers(src, want, sid, did, bd.prefix_dim(), ns, nd, bd.suffix_dim(), bd.elem_size())
+    got = read_layers(gpu, b)
+    for l in range(L):
+        assert np.array_equal(got[l], want[l]), (path, l)
+    assert plan.bytes_per_pair() == bd.bytes_per_token_block_per_layer() * L
+
+
+@pytest.mark.parametrize("elem,suffix", [(1, 37), (2, 37), (4, 5), (8, 3), (2, 1), (1, 1), (2, 8)])
+def test_plan_block_copy_unaligned_suffix_falls_back_to_narrow_vectors(gpu, oracle, elem, suffix):
+    """Odd element counts make chunk starts 1/2/4/8-byte aligned only; result must stay exact (legacy Q8 fixed)."""
+    prefix, ns, nd, L = 2, 6, 5, 2
+    n_src, n_dst = prefix * ns * suffix * elem, prefix * nd * suffix * elem
+    srcs = [DevBuf(gpu, n_src) for _ in range(L)]
+    dsts = [DevBuf(gpu, n_dst) for _ in range(L)]
+    data = [payload(n_src, 40 + l) for l in range(L)]
+    for s, d in zip(srcs, data):
+        s.upload(d)
+    plan = CopyPlan.block_copy_raw([s.ptr for s in srcs], [d.ptr for d in dsts], prefix, ns, nd, suffix, elem)
+    eng = TransferEngine(8)
+    sid, did = [5, 0, 2], [1, 4, 0]
+    eng.run(plan, sid, did, num_layers=L)
+    eng.sync()
+    want = [np.zeros(n_dst, dtype=np.uint8) for _ in range(L)]
+    oracle.copy_blocks_layers(data, want, sid, did, prefix, ns, nd, suffix, elem)
+    for l in range(L):
+        assert np.array_equal(dsts[l].download(), want[l])
+
+
+@pytest.mark.parametrize("path", PATHS)
+@pytest.mark.parametrize("layout", [KvLayout.KvFirst, KvLayout.BlockFirst])
+def test_contig_relayout_and_round_trip(gpu, oracle, path, layout):
+    gpu.set_option("copy_path", path)
+    gpu.set_option("tile_bytes", 2048)
+    L, nb, nc = 4, 9, 6
+    bd = details(layout, L=L, H=2, D=32, bs=16)
+    chunk = bd.bytes_per_token_block_per_layer() // 2
+    ls = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    ls2 = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    contig = KvContiguousBlocks(nc, L, chunk, StorageType.Device(0))
+    src = fill_layers(gpu, ls, 8)
+    sid = [7, 0, 3, 8]
+    cid = [2, 5, 0, 1]
+    eng = TransferEngine(8)
+    eng.run(CopyPlan.contig(ls, contig, True), sid, cid, num_layers=L)
+    eng.sync()
+    want = np.zeros(contig.storage_size(), dtype=np.uint8)
+    oracle.relayout_contig(src, layout.value, nb, chunk, want, sid, cid, True)
+    got = np.empty_like(want)
+    gpu.check(gpu.lib().cuda_memcpy_sync(got.ctypes.data, contig.get_pointer(), got.nbytes))
+    assert np.array_equal(got, want)
+    # and back: contig[cid] -> layers2[sid]; the moved blocks are identical to the originals
+    eng.run(CopyPlan.contig(ls2, contig, False), cid, sid, num_layers=L)
+    eng.sync()
+    want2 = [np.zeros_like(s) for s in src]
+    oracle.relayout_contig(want2, layout.value, nb, chunk, want, cid, sid, False)
+    got2 = read_layers(gpu, ls2)
+    for l in range(L):
+        assert np.array_equal(got2[l], want2[l])
+
+
+def test_layer_range_and_doorbell_like_partial_launch(gpu, oracle):
+    """kvdp_xfer_run moves only [layer_begin, layer_end): the v2 form of per-layer triggering."""
+    L, nb = 5, 6
+    bd = details(KvLayout.KvFirst, L=L)
+    a = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    b = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    src = fill_layers(gpu, a, 2)
+    plan = CopyPlan.block_copy(a, b)
+    eng = TransferEngine(8)
+    eng.run(plan, [0, 1], [3, 4], layer_begin=1, layer_end=3)
+    eng.sync()
+    got = read_layers(gpu, b)
+    want = [np.zeros_like(s) for s in src]
+    oracle.copy_blocks_layers(src[1:3], want[1:3], [0, 1], [3, 4], 2, nb, nb, bd.suffix_dim(), 2)
+    for l in range(L):
+        assert np.array_equal(got[l], want[l])
+    with pytest.raises(Exception, match="layer range"):
+        eng.run(plan, [0], [1], layer_begin=3, layer_end=9)
+
+
+def test_v2_rejects_bad_ids_and_duplicate_destinations(gpu):
+    bd = details(KvLayout.KvFirst, L=2)
+    a = KvBlockStorage.allocate(4, bd, StorageType.Device(0))
+    b = KvBlockStorage.allocate(4, bd, StorageType.Device(0))
+    plan = CopyPlan.block_copy(a, b)
+    eng = TransferEngine(2)
+    with pytest.raises(gpu.KvdpError) as e:
+        eng.run(plan, [0, 1], [2, 2], num_layers=2)
+    assert e.value.code == gpu.KVDP_EDUP
+    with pytest.raises(gpu.KvdpError) as e:
+        eng.run(plan, [0, 4], [2, 3], num_layers=2)
+    assert e.value.code == gpu.KVDP_EINVAL
+    with pytest.raises(gpu.KvdpError):
+        eng.run(plan, [0, -1], [2, 3], num_layers=2)
+    eng.run(plan, [1, 1], [2, 3], num_layers=2)  # repeated SOURCE ids are fine (kv/layer.rs:1536-1537)
+    eng.run(plan, [0, 1, 2], [1, 2, 3], num_layers=2)  # more pairs than announced: staging grows
+    eng.run(plan, [], [], num_layers=2)  # empty is a no-op in v2
+    eng.sync()
+
+
+@pytest.mark.parametrize("path", PATHS)
+def test_completion_flag_published_by_the_kernel(gpu, path):
+    gpu.set_option("copy_path", path)
+    L, nb = 2, 8
+    bd = details(KvLayout.KvFirst, L=L, H=4, D=64, bs=32)
+    a = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    b = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    fill_layers(gpu, a, 4)
+    flag = PinnedBuf(gpu, 64)
+    plan = CopyPlan.block_copy(a, b)
+    eng = TransferEngine(8)
+    for it in range(1, 4):  # the CTA counter must re-arm itself between launches
+        eng.run(plan, list(range(nb)), list(range(nb))[::-1], num_layers=L, done_flag=flag.ptr, done_value=it)
+        eng.sync()
+        assert int(flag.array[:4].view(np.uint32)[0]) == it
+    eng.run(plan, [], [], num_layers=L, done_flag=flag.ptr, done_value=77)  # "notify only" (patch:1373-1377)
+    eng.sync()
+    assert int(flag.array[:4].view(np.uint32)[0]) == 77
+    eng.signal(flag.ptr + 4, 5)
+    eng.sync()
+    assert int(flag.array[4:8].view(np.uint32)[0]) == 5
+    # receiver side: a stream that waits for the flag value
+    dflag = DevBuf(gpu, 4)
+    eng2 = TransferEngine(1)
+    gpu.check(gpu.lib().kvdp_stream_wait_flag(C.c_void_p(eng2.stream), C.c_void_p(dflag.ptr), 3))
+    eng2.signal(flag.ptr + 8, 9)  # ordered after the wait
+    eng.signal(dflag.ptr, 3)      # releases it
+    eng.sync()
+    eng2.sync()
+    assert int(flag.array[8:12].view(np.uint32)[0]) == 9
+
+
+def test_full_size_round_trip_llama8b_isl4k(gpu):
+    """BASELINE config 2 size: Llama-3-8B shape, 64 blocks (512 MiB). Property: layer-separate -> contiguous ->
+    layer-separate (fresh ids) reproduces the source blocks bit-for-bit; every chunk carries a distinct payload."""
+    L, H, D, bs, nb = 32, 8, 128, 64, 64
+    bd = KvBlockDetails(KvLayout.KvFirst, bs, KvModelDetails(L, H, D, DType.BF16))
+    chunk = bd.bytes_per_token_block_per_layer() // 2
+    assert chunk == 128 * 1024
+    a = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    b = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    contig = KvContiguousBlocks(nb, L, chunk, StorageType.Device(0))
+    src = fill_layers(gpu, a, 11)
+    sid = permutation(nb, 1234)
+    cid = permutation(nb, 1235)
+    did = permutation(nb, 1236)
+    eng = TransferEngine(nb)
+    eng.run(CopyPlan.contig(a, contig, True), sid, cid, num_layers=L)
+    eng.run(CopyPlan.contig(b, contig, False), cid, did, num_layers=L)
+    eng.sync()
+    got = read_layers(gpu, b)
+    for l in range(L):
+        s = src[l].reshape(2, nb, chunk)
+        g = got[l].reshape(2, nb, chunk)
+        assert np.array_equal(g[:, did], s[:, sid]), l
