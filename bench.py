@@ -43,7 +43,7 @@ BLOCKS_PER_REQ = 64                    # ISL 4k
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--requests", type=int, default=8, help="requests (of 64 blocks) per step")
@@ -57,47 +57,102 @@ def parse_args():
     ap.add_argument("--no-hash", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-comparators", action="store_true", help="N>1: skip the NCCL / memcpy-peer comparison legs")
     ap.add_argument("--sweep", action="store_true", help="print a table of kernel variants instead of the JSON line")
     return ap.parse_args()
 
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
+    """Samples SM clock, power and throttle reasons through NVML (in-process, every 5 ms) while the timed region runs;
+    falls back to an `nvidia-smi -lms` subprocess when NVML cannot be loaded."""
+
+    def __init__(self, device_index: int):
+        self.idx = device_index
+        self.samples = []          # (sm_mhz, power_w, reasons_bitmask)
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self.thread = None
+        self.nvml = None
+        self.handle = None
+        self.proc = None
+
+    def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            idx = self.idx
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            if vis:
+                try:
+                    idx = int(vis.split(",")[self.idx])
+                except Exception:
+                    pass
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+            return self._start_smi()
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+        self.thread.start()
+
+    def _loop(self):
+        n = self.nvml
+        while not self._stop.is_set():
+            try:
+                mhz = float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+                try:
+                    pw = n.nvmlDeviceGetPowerUsage(self.handle) / 1000.0
+                except Exception:
+                    pw = None
+                try:
+                    rs = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                except Exception:
+                    rs = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+                self.samples.append((mhz, pw, rs))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
     QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, device_index: int):
-        self.idx = device_index
-        self.proc = None
-        self.lines = []
-        self.thread = None
-
-    def start(self):
+    def _start_smi(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
                                           "-i", str(self.idx), "-lms", "100"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
-            return
-        self.thread = threading.Thread(target=self._pump, daemon=True)
-        self.thread.start()
-
-    def _pump(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self._stop.set()
+            self.thread.join(timeout=1)
+            n = self.nvml
+            names = (("hw_slowdown", n.nvmlClocksEventReasonHwSlowdown),
+                     ("hw_thermal_slowdown", n.nvmlClocksEventReasonHwThermalSlowdown),
+                     ("sw_thermal_slowdown", n.nvmlClocksEventReasonSwThermalSlowdown),
+                     ("sw_power_cap", n.nvmlClocksEventReasonSwPowerCap),
+                     ("hw_power_brake", n.nvmlClocksEventReasonHwPowerBrakeSlowdown))
+            reasons = sorted({name for _, _, rs in self.samples for name, bit in names if rs & bit})
+            sm = [s[0] for s in self.samples]
+            pw = [s[1] for s in self.samples if s[1] is not None]
+            return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz,
+                    "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons,
+                    "source": "nvml, 5 ms period, during the timed region"}
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampling unavailable"], "samples": 0}
         self.proc.terminate()
         try:
-            self.proc.wait(timeout=3)
+            out, _ = self.proc.communicate(timeout=3)
         except Exception:
             self.proc.kill()
+            out = ""
         sm, mx, reasons, pw = [], [], set(), []
-        for ln in self.lines:
+        for ln in out.splitlines():
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -111,7 +166,8 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons),
+                "source": "nvidia-smi -lms 100"}
 
 
 # ------------------------------------------------------------------------------------------------ CPU legs (oracle)

@@ -10,12 +10,14 @@
 // written here from the specification, not from any implementation's source.
 //
 // Launch structure for one ragged batch (CSR offsets):
-//   1. kvdp_block_count_scan_*  : block_offsets[r] = sum_{q<r} len_q / block_size       (3 tiny kernels)
+//   1. kvdp_block_count_scan_*  : block_offsets[r] = sum_{q<r} len_q / block_size       (1 CTA up to 64K requests,
+//                                 else partials / spine / apply)
 //   2. kvdp_hash_blocks_*       : one thread per token block. Fast path (256/512-byte blocks): each lane pulls its
 //                                 own block into a padded shared-memory row with one cp.async.bulk (TMA), so global
 //                                 reads are full-line and shared reads are conflict-free 16-byte loads; the seed-derived
 //                                 secret words arrive through the kernel-parameter constant bank.
-//   3. kvdp_hash_chain          : one thread per request walks its blocks (16-byte XXH3 per step, serial by nature).
+//   3. kvdp_hash_chain          : one thread per request walks its blocks (16-byte XXH3 per step, serial by nature;
+//                                 a register ring prefetches the next 8 block hashes to hide the loads).
 // HBM-bound by design: 4*block_size bytes read + 16 bytes written per block; no tensor cores (nothing contracts).
 #include <string.h>
 
@@ -324,21 +326,52 @@ __global__ void __launch_bounds__(256) kvdp_hash_blocks_generic(const __grid_con
 }
 
 // ------------------------------------------------------------------------------------------------ chain
-__global__ void __launch_bounds__(128) kvdp_hash_chain(const __grid_constant__ HashArgs A,
-                                                       const __grid_constant__ HashSecrets S) {
+// One thread per request. The chain is serial by construction (each step hashes the previous step's result), so the
+// kernel is latency-bound on the longest request; what can be hidden is the load of the block hashes: a register
+// ring keeps the next kChainAhead values in flight while the current ones are chained. (A warp-per-request variant
+// with shuffled inputs was measured 2x slower: 32 lanes repeating the same 64-bit multiplies made it issue-bound.)
+constexpr int kChainThreads = 64;
+constexpr int kChainAhead = 8;
+__global__ void __launch_bounds__(kChainThreads) kvdp_hash_chain(const __grid_constant__ HashArgs A,
+                                                                 const __grid_constant__ HashSecrets S) {
   const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= A.n_req) return;
   const int64_t b0 = __ldg(A.block_offsets + r), b1 = __ldg(A.block_offsets + r + 1);
-  uint64_t parent = 0;
-  for (int64_t b = b0; b < b1; ++b) {
-    const uint64_t bh = A.block_hash[b];
-    uint64_t sh;
-    if (b == b0 && !(A.flags & KVDP_HASH_TWIN_FIRST))
-      sh = bh;
-    else
-      sh = xxh3_16(parent, bh, S);
-    A.seq_hash[b] = sh;
-    parent = sh;
+  if (b0 >= b1) return;
+  const uint64_t* __restrict__ bh = A.block_hash + b0;
+  uint64_t* __restrict__ sq = A.seq_hash + b0;
+  const uint32_t n = (uint32_t)(b1 - b0);  // blocks of one request always fit 32 bits
+  // first block: its sequence hash is its block hash (twin variant: chained onto parent 0)
+  uint64_t parent = bh[0];
+  if (A.flags & KVDP_HASH_TWIN_FIRST) parent = xxh3_16(0, parent, S);
+  sq[0] = parent;
+  uint32_t i = 1;
+  if (n >= 1 + 2 * kChainAhead) {
+    uint64_t cur[kChainAhead], nxt[kChainAhead];
+#pragma unroll
+    for (int k = 0; k < kChainAhead; ++k) cur[k] = bh[i + k];
+    // main loop: groups of kChainAhead with the next group's loads already in flight, no bounds predicates
+    for (; i + 2 * kChainAhead <= n; i += kChainAhead) {
+#pragma unroll
+      for (int k = 0; k < kChainAhead; ++k) nxt[k] = bh[i + kChainAhead + k];
+#pragma unroll
+      for (int k = 0; k < kChainAhead; ++k) {
+        parent = xxh3_16(parent, cur[k], S);
+        sq[i + k] = parent;
+      }
+#pragma unroll
+      for (int k = 0; k < kChainAhead; ++k) cur[k] = nxt[k];
+    }
+#pragma unroll
+    for (int k = 0; k < kChainAhead; ++k) {  // the last prefetched group
+      parent = xxh3_16(parent, cur[k], S);
+      sq[i + k] = parent;
+    }
+    i += kChainAhead;
+  }
+  for (; i < n; ++i) {
+    parent = xxh3_16(parent, bh[i], S);
+    sq[i] = parent;
   }
 }
 
@@ -433,6 +466,47 @@ __global__ void __launch_bounds__(kScanThreads) kvdp_block_count_scan_apply(cons
   }
 }
 
+// Small batches (<= kScanSmallMax requests): one CTA scans everything, one launch instead of three.
+constexpr int kScanSmallThreads = 1024;
+constexpr int64_t kScanSmallMax = 1 << 16;
+__global__ void __launch_bounds__(kScanSmallThreads) kvdp_block_count_scan_small(const int64_t* __restrict__ offsets,
+                                                                                 int64_t n_req, int32_t bs,
+                                                                                 int64_t* __restrict__ block_offsets) {
+  __shared__ int64_t warp_sums[kScanSmallThreads / 32];
+  __shared__ int64_t carry_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (int64_t base = 0; base <= n_req; base += kScanSmallThreads) {
+    const int64_t r = base + threadIdx.x;  // coalesced: consecutive threads read consecutive offsets
+    const int64_t v = req_blocks(offsets, r, n_req, bs);
+    int64_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int64_t o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int64_t w = warp_sums[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int64_t o = __shfl_up_sync(0xffffffffu, w, d);
+        if (lane >= d) w += o;
+      }
+      warp_sums[lane] = w;
+    }
+    __syncthreads();
+    const int64_t carry = carry_s;
+    const int64_t ex = carry + (warp ? warp_sums[warp - 1] : 0) + incl - v;
+    if (r <= n_req) block_offsets[r] = ex;
+    __syncthreads();
+    if (threadIdx.x == kScanSmallThreads - 1) carry_s = carry + warp_sums[31];
+    __syncthreads();
+  }
+}
+
 __global__ void kvdp_xxh3_batch_kernel(const uint8_t* __restrict__ data, int64_t n, int64_t len, uint64_t* out,
                                        const __grid_constant__ HashSecrets S) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -479,10 +553,15 @@ int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, i
   // 1. block offsets
   int64_t* partials = (int64_t*)d_workspace;
   const int64_t tiles = (n_req + 1 + kScanTile - 1) / kScanTile;
-  kvdp_block_count_scan_partials<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size, partials);
-  kvdp_block_count_scan_spine<<<1, kScanThreads, 0, stream>>>(partials, tiles);
-  kvdp_block_count_scan_apply<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size, partials,
-                                                                            d_block_offsets);
+  if (n_req + 1 <= kScanSmallMax) {
+    kvdp_block_count_scan_small<<<1, kScanSmallThreads, 0, stream>>>(d_offsets, n_req, block_size, d_block_offsets);
+  } else {
+    kvdp_block_count_scan_partials<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size,
+                                                                                 partials);
+    kvdp_block_count_scan_spine<<<1, kScanThreads, 0, stream>>>(partials, tiles);
+    kvdp_block_count_scan_apply<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size, partials,
+                                                                              d_block_offsets);
+  }
   KVDP_CUDA(cudaGetLastError());
 
   const int64_t max_blocks = total_tokens / block_size;
@@ -533,7 +612,7 @@ int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, i
 
   // 3. chain
   if (d_seq_hash) {
-    kvdp_hash_chain<<<(unsigned)((n_req + 127) / 128), 128, 0, stream>>>(A, S);
+    kvdp_hash_chain<<<(unsigned)((n_req + kChainThreads - 1) / kChainThreads), kChainThreads, 0, stream>>>(A, S);
     KVDP_CUDA(cudaGetLastError());
   }
   return 0;
