@@ -57,6 +57,9 @@ def parse_args():
     ap.add_argument("--no-hash", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--mode", default="both", choices=["both", "push", "pull"],
+                    help="N>1: push = prefill-side kernel stores into the decode GPU; pull = decode-side kernel loads "
+                         "from the prefill GPU; both = measure both, headline the faster")
     ap.add_argument("--no-comparators", action="store_true", help="N>1: skip the NCCL / memcpy-peer comparison legs")
     ap.add_argument("--sweep", action="store_true", help="print a table of kernel variants instead of the JSON line")
     return ap.parse_args()

@@ -1,21 +1,23 @@
-"""bench_multi.py — the N>1 arm of bench.py: prefill GPUs push KV blocks into decode GPUs over NVLink.
+"""bench_multi.py — the N>1 arm of bench.py: KV blocks move from prefill GPUs to decode GPUs over NVLink.
 
-Ranks [0, P) are prefill, ranks [P, N) decode (P = N // 2). Prefill rank r owns a layer-separate Llama-3-8B-shaped cache
-and pushes each step's batch (R requests x 64 blocks) straight into the contiguous-per-block cache of decode rank
-P + r % D: the relayout kernel's stores go to the peer-mapped destination (CUDA IPC), and the last CTA publishes a
-completion flag in the decode GPU's memory. No NCCL on the data path; NCCL send/recv of the same payload is timed
-beside it as the comparison the north star names, and a plain cudaMemcpyAsync to the peer as the link's practical ceiling.
+Ranks [0, P) are prefill, ranks [P, N) decode (P = N // 2); prefill rank r is paired with decode rank P + r % D.
+Each step moves one batch (R requests x 64 Llama-3-8B-shaped blocks) from the prefill GPU's layer-separate cache into
+the decode GPU's contiguous-per-block cache with ONE launch of the relayout kernel, addressing the other GPU's memory
+through CUDA-IPC peer mappings, and the kernel's last CTA publishes a completion flag in the other GPU's memory:
+  push : the kernel runs on the prefill GPU and STORES into the decode cache  (the reference's NIXL WRITE, write_blocks)
+  pull : the kernel runs on the decode GPU and LOADS from the prefill cache   (the reference's NIXL READ, read_blocks)
+No NCCL on the data path. NCCL send/recv of the same payload (the comparison the north star names) and a plain
+cudaMemcpyAsync to the peer (the link's practical ceiling) are timed beside it.
 """
 from __future__ import annotations
 
 import ctypes as C
 import json
-import os
 
 import numpy as np
 
 from bench import BLOCK_BYTES, BLOCKS_PER_REQ, CHUNK, GB, L8B, ClockSampler, workload_config
-from bench_single import Setup, measured_peaks
+from bench_single import Setup
 
 NVLINK_PEAK_MEASURED = 770.0   # GB/s per direction per GPU, peer copy (B200_PROFILING.md)
 NVLINK_PEAK_NOMINAL = 900.0
@@ -37,49 +39,71 @@ def run_multi(args, rank, local_rank, world):
     P = world // 2
     D = world - P
     is_prefill = rank < P
-    peer = (P + rank % D) if is_prefill else None
-    senders = [r for r in range(P) if P + r % D == rank] if not is_prefill else []
+    partner = (P + rank % D) if is_prefill else [r for r in range(P) if P + r % D == rank][0]
     pairs = BLOCKS_PER_REQ * args.requests
     n = args.cache_blocks
+    steps, warmup = args.steps, args.warmup
 
-    # ---- decode side: destination cache + flag, exported over CUDA IPC
-    handles = {"cache": None, "flag": None}
-    dst_ptr = C.c_void_p()
+    def export(ptr):
+        h = (C.c_uint8 * lib.IPC_HANDLE_BYTES)()
+        lib.check(L.kvdp_ipc_export(ptr, h))
+        return bytes(h)
+
+    def imp(hbytes):
+        hb = (C.c_uint8 * lib.IPC_HANDLE_BYTES).from_buffer_copy(hbytes)
+        p = C.c_void_p()
+        lib.check(L.kvdp_ipc_import(hb, local_rank, C.byref(p)))
+        return p
+
+    # ---- memory the other side must reach: allocated by libkvdp (cudaMalloc) and exported over CUDA IPC
     flag_ptr = C.c_void_p()
-    if not is_prefill:
-        lib.check(L.kvdp_device_alloc(C.byref(dst_ptr), n * BLOCK_BYTES, local_rank))
-        lib.check(L.kvdp_device_alloc(C.byref(flag_ptr), 256, local_rank))
-        h1 = (C.c_uint8 * lib.IPC_HANDLE_BYTES)()
-        h2 = (C.c_uint8 * lib.IPC_HANDLE_BYTES)()
-        lib.check(L.kvdp_ipc_export(dst_ptr, h1))
-        lib.check(L.kvdp_ipc_export(flag_ptr, h2))
-        handles = {"cache": bytes(h1), "flag": bytes(h2)}
+    lib.check(L.kvdp_device_alloc(C.byref(flag_ptr), 256, local_rank))
+    handles = {"flag": export(flag_ptr)}
+    own_layers, own_cache = [], C.c_void_p()
+    if is_prefill:
+        g = torch.Generator(device="cuda")
+        g.manual_seed(42 + rank)
+        for _ in range(L8B):
+            p = C.c_void_p()
+            lib.check(L.kvdp_device_alloc(C.byref(p), 2 * n * CHUNK, local_rank))
+            torch.as_tensor(CudaArray(p.value, 2 * n * CHUNK), device="cuda").random_(0, 256, generator=g)
+            own_layers.append(p)
+        handles["layers"] = [export(p) for p in own_layers]
+    else:
+        lib.check(L.kvdp_device_alloc(C.byref(own_cache), n * BLOCK_BYTES, local_rank))
+        handles["cache"] = export(own_cache)
     all_handles = [None] * world
     dist.all_gather_object(all_handles, handles)
-
-    setup = None
-    peer_dst = C.c_void_p()
-    peer_flag = C.c_void_p()
+    peer_flag = imp(all_handles[partner]["flag"])
     if is_prefill:
-        hb = (C.c_uint8 * lib.IPC_HANDLE_BYTES).from_buffer_copy(all_handles[peer]["cache"])
-        fb = (C.c_uint8 * lib.IPC_HANDLE_BYTES).from_buffer_copy(all_handles[peer]["flag"])
-        lib.check(L.kvdp_ipc_import(hb, local_rank, C.byref(peer_dst)))
-        lib.check(L.kvdp_ipc_import(fb, local_rank, C.byref(peer_flag)))
-        setup = Setup(args, torch, lib, device=local_rank, dst_contig_ptr=peer_dst.value, dst_blocks=n)
+        peer_cache = imp(all_handles[partner]["cache"])
+        setup = Setup(args, torch, lib, device=local_rank, dst_contig_ptr=peer_cache.value, dst_blocks=n,
+                      src_ptrs=[p.value for p in own_layers])           # push plan
+    else:
+        peer_layers = [imp(h).value for h in all_handles[partner]["layers"]]
+        setup = Setup(args, torch, lib, device=local_rank, dst_contig_ptr=own_cache.value, dst_blocks=n,
+                      src_ptrs=peer_layers)                             # pull plan
+    wait_stream = torch.cuda.Stream()
     dist.barrier()
+    seq = {"v": 0}
 
-    steps, warmup = args.steps, args.warmup
-    my_stream = torch.cuda.Stream()
-
-    def timed_region(run_step, total_steps):
-        """Barrier + sync both sides, device events, MAX over ranks. Decode ranks wait for the last flag value."""
+    def timed(mode, k0, count):
+        """Barrier + device sync on both sides, CUDA events on the launching stream, MAX over ranks. The passive side
+        stream-waits on the completion flag the kernel's last CTA writes into its memory."""
+        runner = is_prefill if mode == "push" else not is_prefill
         torch.cuda.synchronize()
         dist.barrier()
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        st = setup.stream if is_prefill else my_stream
+        st = setup.stream if runner else wait_stream
         a.record(st)
-        run_step()
+        if runner:
+            for k in range(count):
+                seq["v"] += 1
+                setup.step(k0 + k, done_flag=peer_flag, done_value=seq["v"])
+        else:
+            seq["v"] += count
+            lib.check(L.kvdp_stream_wait_flag(C.c_void_p(wait_stream.cuda_stream), flag_ptr, seq["v"]))
         b.record(st)
         torch.cuda.synchronize()
         dist.barrier()
@@ -87,135 +111,133 @@ def run_multi(args, rank, local_rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- fused push: relayout kernel storing into the peer cache, in-kernel completion flag
-    seq = {"v": 0}
-
-    def push_steps(k0, count):
-        def fn():
-            if is_prefill:
-                for k in range(count):
-                    seq["v"] += 1
-                    # senders that share a decode rank would need one flag each; with P == D every flag has one writer
-                    setup.step(k0 + k, done_flag=peer_flag, done_value=seq["v"])
-            else:
-                seq["v"] += count
-                lib.check(L.kvdp_stream_wait_flag(C.c_void_p(my_stream.cuda_stream), flag_ptr, seq["v"]))
-        return fn
-
-    timed_region(push_steps(0, warmup), warmup)
-    clocks = ClockSampler(local_rank)
-    clocks.start()
-    sec = timed_region(push_steps(warmup, steps), steps)
-    clk = clocks.stop()
-    total_payload = P * pairs * BLOCK_BYTES * steps
-    value = total_payload / sec / GB
-    per_link = pairs * BLOCK_BYTES * steps / sec / GB * (max(1, P // D))
-
-    # ---- correctness spot check: prefill sends sampled source chunks over NCCL; decode compares with its cache
-    ok = torch.ones(1, dtype=torch.int32, device="cuda")
-    last = warmup + steps - 1
-    samples = 4
-    if is_prefill:
-        s_ids, d_ids = setup.ids(last)
-        rng = np.random.Generator(np.random.PCG64(last))
-        for _ in range(samples):
-            i, l, kv = int(rng.integers(pairs)), int(rng.integers(L8B)), int(rng.integers(2))
-            src = setup.src_layers[l][(kv * n + int(s_ids[i])) * CHUNK:(kv * n + int(s_ids[i]) + 1) * CHUNK]
-            meta = torch.tensor([int(d_ids[i]), l, kv], dtype=torch.int64, device="cuda")
-            dist.send(meta, peer)
-            dist.send(src.contiguous(), peer)
-    else:
-        cache = torch.as_tensor(CudaArray(dst_ptr.value, n * BLOCK_BYTES), device="cuda")
-        for s in senders:
+    def verify(mode, step, samples=4):
+        """Runner announces sampled (src id, dst id, layer, kv); prefill ships the source chunk; decode compares."""
+        runner = is_prefill if mode == "push" else not is_prefill
+        ok = torch.ones(1, dtype=torch.int32, device="cuda")
+        meta = torch.zeros(samples * 4, dtype=torch.int64, device="cuda")
+        if runner:
+            s_ids, d_ids = setup.ids(step)
+            rng = np.random.Generator(np.random.PCG64(step))
+            rows = []
             for _ in range(samples):
-                meta = torch.empty(3, dtype=torch.int64, device="cuda")
+                i = int(rng.integers(pairs))
+                rows += [int(s_ids[i]), int(d_ids[i]), int(rng.integers(L8B)), int(rng.integers(2))]
+            meta = torch.tensor(rows, dtype=torch.int64, device="cuda")
+            dist.send(meta, partner)
+        else:
+            dist.recv(meta, partner)
+        rows = meta.tolist()
+        for j in range(samples):
+            s, d, l, kv = rows[4 * j:4 * j + 4]
+            if is_prefill:
+                layer = torch.as_tensor(CudaArray(own_layers[l].value, 2 * n * CHUNK), device="cuda")
+                dist.send(layer[(kv * n + s) * CHUNK:(kv * n + s + 1) * CHUNK].contiguous(), partner)
+            else:
                 buf = torch.empty(CHUNK, dtype=torch.uint8, device="cuda")
-                dist.recv(meta, s)
-                dist.recv(buf, s)
-                d, l, kv = [int(x) for x in meta.tolist()]
+                dist.recv(buf, partner)
+                cache = torch.as_tensor(CudaArray(own_cache.value, n * BLOCK_BYTES), device="cuda")
                 off = d * BLOCK_BYTES + (l * 2 + kv) * CHUNK
                 if not torch.equal(buf, cache[off:off + CHUNK]):
                     ok.zero_()
-    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-    if int(ok.item()) != 1:
-        raise RuntimeError("peer push result differs from its source")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) != 1:
+            raise RuntimeError("%s result differs from its source" % mode)
+
+    modes = ["push", "pull"] if args.mode == "both" else [args.mode]
+    results, clk = {}, None
+    for mode in modes:
+        if not is_prefill:
+            lib.check(L.kvdp_memset(own_cache, 0, n * BLOCK_BYTES))  # each mode must fill the cache itself
+        timed(mode, 0, warmup)
+        clocks = ClockSampler(local_rank)
+        clocks.start()
+        sec = timed(mode, warmup, steps)
+        c = clocks.stop()
+        clk = clk or c
+        verify(mode, warmup + steps - 1)
+        results[mode] = {"value": P * pairs * BLOCK_BYTES * steps / sec / GB, "sec": sec,
+                         "per_direction": pairs * BLOCK_BYTES * steps / sec / GB * max(1, P // D)}
 
     # ---- comparators: (i) local relayout into HBM staging + NCCL send/recv, (ii) plain peer memcpy of the payload
-    nsteps_c = max(2, min(steps, 10))
-    staging = torch.empty(pairs * BLOCK_BYTES, dtype=torch.uint8, device="cuda")
-    nccl_plan = C.c_void_p()
-    if is_prefill:
-        lib.check(L.kvdp_plan_contig(C.byref(nccl_plan), setup.src_ptrs.ctypes.data, L8B, 0, n, CHUNK,
-                                     C.c_void_p(staging.data_ptr()), pairs, 1, local_rank))
-    iota = np.arange(pairs, dtype=np.int32)
-
-    def nccl_steps():
-        cur = torch.cuda.current_stream()
-        for k in range(nsteps_c):
-            if is_prefill:
-                s_ids, _ = setup.ids(k)
-                lib.check(L.kvdp_xfer_run(setup.xfer, nccl_plan, s_ids.ctypes.data, iota.ctypes.data, pairs, 0, L8B, 0,
-                                          None, 0))
-                ev = torch.cuda.Event()
-                ev.record(setup.stream)
-                cur.wait_event(ev)
-                dist.send(staging, peer)
-                ev2 = torch.cuda.Event()
-                ev2.record(cur)
-                setup.stream.wait_event(ev2)
-            else:
-                for s in senders:
-                    dist.recv(staging, s)
-
-    def timed_default_stream(fn):
-        torch.cuda.synchronize()
-        dist.barrier()
-        torch.cuda.synchronize()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        fn()
-        b.record()
-        torch.cuda.synchronize()
-        dist.barrier()
-        t = torch.tensor([a.elapsed_time(b) / 1e3], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
     nccl_value = memcpy_value = None
+    nsteps_c = max(2, min(steps, 10))
     if not args.no_comparators:
-        nccl_steps()  # warm-up (NCCL connection setup)
-        t_nccl = timed_default_stream(nccl_steps)
-        nccl_value = P * pairs * BLOCK_BYTES * nsteps_c / t_nccl / GB
-
-    def memcpy_steps():
+        staging = torch.empty(pairs * BLOCK_BYTES, dtype=torch.uint8, device="cuda")
+        iota = np.arange(pairs, dtype=np.int32)
+        nccl_plan = C.c_void_p()
         if is_prefill:
-            for _ in range(nsteps_c):
-                lib.check(L.cuda_memcpy_async(peer_dst, C.c_void_p(staging.data_ptr()), pairs * BLOCK_BYTES,
-                                              C.c_void_p(torch.cuda.current_stream().cuda_stream)))
-    if not args.no_comparators:
+            ptrs = np.array([p.value for p in own_layers], dtype=np.uint64)
+            lib.check(L.kvdp_plan_contig(C.byref(nccl_plan), ptrs.ctypes.data, L8B, 0, n, CHUNK,
+                                         C.c_void_p(staging.data_ptr()), pairs, 1, local_rank))
+
+        def nccl_steps():
+            cur = torch.cuda.current_stream()
+            for k in range(nsteps_c):
+                if is_prefill:
+                    s_ids, _ = setup.ids(k)
+                    lib.check(L.kvdp_xfer_run(setup.xfer, nccl_plan, s_ids.ctypes.data, iota.ctypes.data, pairs, 0,
+                                              L8B, 0, None, 0))
+                    ev = torch.cuda.Event()
+                    ev.record(setup.stream)
+                    cur.wait_event(ev)
+                    dist.send(staging, partner)
+                    ev2 = torch.cuda.Event()
+                    ev2.record(cur)
+                    setup.stream.wait_event(ev2)
+                else:
+                    dist.recv(staging, partner)
+
+        def memcpy_steps():
+            if is_prefill:
+                for _ in range(nsteps_c):
+                    lib.check(L.cuda_memcpy_async(peer_cache, C.c_void_p(staging.data_ptr()), pairs * BLOCK_BYTES,
+                                                  C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+
+        def timed_default_stream(fn):
+            torch.cuda.synchronize()
+            dist.barrier()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            dist.barrier()
+            t = torch.tensor([a.elapsed_time(b) / 1e3], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        nccl_steps()  # warm-up (NCCL connection setup)
+        nccl_value = P * pairs * BLOCK_BYTES * nsteps_c / timed_default_stream(nccl_steps) / GB
         memcpy_steps()
-        t_cpy = timed_default_stream(memcpy_steps)
-        memcpy_value = P * pairs * BLOCK_BYTES * nsteps_c / t_cpy / GB
+        memcpy_value = P * pairs * BLOCK_BYTES * nsteps_c / timed_default_stream(memcpy_steps) / GB
 
     if rank == 0:
-        peak, peak_src = measured_peaks()
+        best = max(results, key=lambda m: results[m]["value"])
+        r = results[best]
         cfg = workload_config(args)
-        cfg["pairs"] = ["%d->%d" % (r, P + r % D) for r in range(P)]
+        cfg["pairs"] = ["%d->%d" % (q, P + q % D) for q in range(P)]
+        cfg["mode"] = best
         line = {
-            "metric": "kv_transfer_GBps", "value": value, "unit": "GB/s", "n_gpus": world, "steps": steps,
-            "warmup": warmup, "ms_per_step": sec / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "metric": "kv_transfer_GBps", "value": r["value"], "unit": "GB/s", "n_gpus": world, "steps": steps,
+            "warmup": warmup, "ms_per_step": r["sec"] / steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
-            "blocks_per_s": P * pairs * steps / sec,
-            "roofline": {"bound": "nvlink", "achieved": per_link, "peak": NVLINK_PEAK_MEASURED, "unit": "GB/s",
-                         "frac": per_link / NVLINK_PEAK_MEASURED, "traffic": None,
-                         "kernel": "kvdp_copy_tma_in_kernel / kvdp_copy_vec_kernel (peer stores)",
+            "blocks_per_s": P * pairs * steps / r["sec"],
+            "modes": {m: {"value": v["value"], "per_direction_GBps": v["per_direction"],
+                          "frac_of_nominal_900": v["per_direction"] / NVLINK_PEAK_NOMINAL,
+                          "frac_of_measured_770": v["per_direction"] / NVLINK_PEAK_MEASURED}
+                      for m, v in results.items()},
+            "roofline": {"bound": "nvlink", "achieved": r["per_direction"], "peak": NVLINK_PEAK_MEASURED,
+                         "unit": "GB/s", "frac": r["per_direction"] / NVLINK_PEAK_MEASURED, "traffic": None,
+                         "kernel": "kvdp_copy_tma_tma_kernel over peer-mapped memory (%s)" % best,
                          "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
-                         "frac_of_nominal_900": per_link / NVLINK_PEAK_NOMINAL,
+                         "frac_of_nominal_900": r["per_direction"] / NVLINK_PEAK_NOMINAL,
                          "note": "achieved = wire bytes per direction on the busiest port / time"},
             "comparators": {"nccl_send_recv_GBps": nccl_value, "cuda_memcpy_peer_GBps": memcpy_value,
                             "steps": nsteps_c},
             "options": {k: lib.get_option(k) for k in ("copy_path", "tile_bytes", "stages", "ctas_per_sm")},
-            "gpu_launches": steps, "clocks": clk,
+            "gpu_launches": steps * len(modes), "clocks": clk,
             "e2e": {"value": None, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                     "note": "see the N=1 line: the host-buffer path is PCIe-bound per GPU and does not cross NVLink"},
         }

@@ -37,18 +37,21 @@ def ncu_traffic(kernel_key: str):
 class Setup:
     """8 GiB layer-separate source cache + 8 GiB contiguous destination cache on cuda:0 (torch owns the memory)."""
 
-    def __init__(self, args, torch, lib, device=0, dst_contig_ptr=None, dst_blocks=None):
+    def __init__(self, args, torch, lib, device=0, dst_contig_ptr=None, dst_blocks=None, src_ptrs=None):
         self.torch, self.lib, self.args = torch, lib, args
         n = args.cache_blocks
         self.n = n
-        g = torch.Generator(device="cuda")
-        g.manual_seed(42 + device)
         self.src_layers = []
-        for l in range(L8B):
-            t = torch.empty(2 * n * CHUNK, dtype=torch.uint8, device="cuda")
-            t.random_(0, 256, generator=g)
-            self.src_layers.append(t)
-        self.src_ptrs = np.array([t.data_ptr() for t in self.src_layers], dtype=np.uint64)
+        if src_ptrs is None:
+            g = torch.Generator(device="cuda")
+            g.manual_seed(42 + device)
+            for l in range(L8B):
+                t = torch.empty(2 * n * CHUNK, dtype=torch.uint8, device="cuda")
+                t.random_(0, 256, generator=g)
+                self.src_layers.append(t)
+            self.src_ptrs = np.array([t.data_ptr() for t in self.src_layers], dtype=np.uint64)
+        else:
+            self.src_ptrs = np.asarray(src_ptrs, dtype=np.uint64)  # e.g. peer-mapped layers (pull mode)
         if dst_contig_ptr is None:
             self.dst = torch.zeros(n * BLOCK_BYTES, dtype=torch.uint8, device="cuda")
             dst_contig_ptr, dst_blocks = self.dst.data_ptr(), n
@@ -213,25 +216,46 @@ def hash_bench(torch, lib, steps, warmup, peak):
     d_sh = torch.empty(nblk, dtype=torch.int64, device="cuda")
     ws_bytes = L.kvdp_hash_workspace_bytes(n_req)
     d_ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
-    st = torch.cuda.current_stream()
+    # Two streams, alternating batches, each with its own outputs: the serial chain kernel of batch k (latency-bound,
+    # a few hundred warps) overlaps the HBM-bound block-hash kernel of batch k+1, as a router streaming 1M requests
+    # through in batches would run it.
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    outs = [(d_boff, d_bh, d_sh, d_ws)]
+    outs.append((torch.empty_like(d_boff), torch.empty_like(d_bh), torch.empty_like(d_sh), torch.empty_like(d_ws)))
 
-    def run(salt):
-        lib.check(L.kvdp_hash_token_blocks(tok.data_ptr(), d_off.data_ptr(), n_req, total, BS, salt, d_boff.data_ptr(),
-                                           d_bh.data_ptr(), d_sh.data_ptr(), d_ws.data_ptr(), ws_bytes, 0,
+    def run(salt, k=0):
+        st = streams[k & 1]
+        boff, bh, sh, ws = outs[k & 1]
+        lib.check(L.kvdp_hash_token_blocks(tok.data_ptr(), d_off.data_ptr(), n_req, total, BS, salt, boff.data_ptr(),
+                                           bh.data_ptr(), sh.data_ptr(), ws.data_ptr(), ws_bytes, 0,
                                            C.c_void_p(st.cuda_stream)))
-    for _ in range(warmup):
-        run(1337)
     torch.cuda.synchronize()
+    for k in range(warmup):
+        run(1337, k)
+    torch.cuda.synchronize()
+    # (1) latency of one batch on one stream
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record(st)
+    a.record(streams[0])
     for k in range(steps):
-        run(1337 + k)
-    b.record(st)
+        run(1337 + k, 0)
+    b.record(streams[0])
     torch.cuda.synchronize()
-    sec = a.elapsed_time(b) / 1e3 / steps
-    # spot parity inside the bench: first request of the last run against python-free re-hash on a second salt run
+    sec_serial = a.elapsed_time(b) / 1e3 / steps
+    # (2) throughput with batches alternating over the two streams
+    start = torch.cuda.Event(enable_timing=True)
+    ends = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
+    start.record(streams[0])
+    streams[1].wait_event(start)
+    n_pipe = 2 * steps
+    for k in range(n_pipe):
+        run(1337 + k, k)
+    ends[0].record(streams[0])
+    ends[1].record(streams[1])
+    torch.cuda.synchronize()
+    sec = max(start.elapsed_time(ends[0]), start.elapsed_time(ends[1])) / 1e3 / n_pipe
     out = {"hashes_per_s": nblk / sec, "tokens_per_s": total / sec, "ms_per_batch": sec * 1e3, "requests": n_req,
-           "blocks": nblk, "launches_per_batch": 3,
+           "blocks": nblk, "launches_per_batch": 3, "streams": 2,
+           "single_stream": {"hashes_per_s": nblk / sec_serial, "ms_per_batch": sec_serial * 1e3},
            "roofline": {"bound": "hbm", "achieved": nblk * 272 / sec / GB, "peak": peak, "unit": "GB/s",
                         "frac": nblk * 272 / sec / GB / peak, "traffic": ncu_traffic("kvdp_hash_blocks_tma")}}
     # e2e: pinned host tokens -> device -> hashes back on the host, through kvdp_hash_token_blocks_host

@@ -466,44 +466,43 @@ __global__ void __launch_bounds__(kScanThreads) kvdp_block_count_scan_apply(cons
   }
 }
 
-// Small batches (<= kScanSmallMax requests): one CTA scans everything, one launch instead of three.
+// Small batches (<= kScanSmallMax requests): one CTA scans everything in one pass, one launch instead of three.
+// Each thread owns a run of consecutive requests: sum them, one block-wide exclusive scan of the per-thread sums,
+// then a second walk over the same (now cached) offsets writes the per-request prefix.
 constexpr int kScanSmallThreads = 1024;
 constexpr int64_t kScanSmallMax = 1 << 16;
 __global__ void __launch_bounds__(kScanSmallThreads) kvdp_block_count_scan_small(const int64_t* __restrict__ offsets,
                                                                                  int64_t n_req, int32_t bs,
                                                                                  int64_t* __restrict__ block_offsets) {
   __shared__ int64_t warp_sums[kScanSmallThreads / 32];
-  __shared__ int64_t carry_s;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry_s = 0;
+  const int64_t per = (n_req + 1 + kScanSmallThreads - 1) / kScanSmallThreads;
+  const int64_t r0 = (int64_t)threadIdx.x * per;
+  int64_t s = 0;
+  for (int64_t i = 0; i < per; ++i) s += req_blocks(offsets, r0 + i, n_req, bs);
+  int64_t incl = s;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int64_t o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += o;
+  }
+  if (lane == 31) warp_sums[warp] = incl;
   __syncthreads();
-  for (int64_t base = 0; base <= n_req; base += kScanSmallThreads) {
-    const int64_t r = base + threadIdx.x;  // coalesced: consecutive threads read consecutive offsets
-    const int64_t v = req_blocks(offsets, r, n_req, bs);
-    int64_t incl = v;
+  if (warp == 0) {
+    int64_t w = warp_sums[lane];
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-      const int64_t o = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= d) incl += o;
+      const int64_t o = __shfl_up_sync(0xffffffffu, w, d);
+      if (lane >= d) w += o;
     }
-    if (lane == 31) warp_sums[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-      int64_t w = warp_sums[lane];
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const int64_t o = __shfl_up_sync(0xffffffffu, w, d);
-        if (lane >= d) w += o;
-      }
-      warp_sums[lane] = w;
-    }
-    __syncthreads();
-    const int64_t carry = carry_s;
-    const int64_t ex = carry + (warp ? warp_sums[warp - 1] : 0) + incl - v;
-    if (r <= n_req) block_offsets[r] = ex;
-    __syncthreads();
-    if (threadIdx.x == kScanSmallThreads - 1) carry_s = carry + warp_sums[31];
-    __syncthreads();
+    warp_sums[lane] = w;
+  }
+  __syncthreads();
+  int64_t run = (warp ? warp_sums[warp - 1] : 0) + incl - s;
+  for (int64_t i = 0; i < per; ++i) {
+    const int64_t r = r0 + i;
+    if (r <= n_req) block_offsets[r] = run;
+    run += req_blocks(offsets, r, n_req, bs);
   }
 }
 
