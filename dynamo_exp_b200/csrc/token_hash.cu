@@ -584,22 +584,22 @@ int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, i
   if (len == 256) {
     constexpr int W = 8;
     const size_t smem = (size_t)W * 32 * (256 + 16) + 8 * W;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};  // the attribute is per device
+    if (dev >= 64 || !attr_set[dev]) {
       KVDP_CUDA(cudaFuncSetAttribute(kvdp_hash_blocks_tma<4, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)smem));
-      attr_set = true;
+      if (dev < 64) attr_set[dev] = true;
     }
     const int64_t grid = std::min<int64_t>((warp_tiles + W - 1) / W, (int64_t)di.sm_count * 3);
     kvdp_hash_blocks_tma<4, W><<<(unsigned)std::max<int64_t>(grid, 1), W * 32, smem, stream>>>(A, S);
   } else if (len == 512) {
     constexpr int W = 4;
     const size_t smem = (size_t)W * 32 * (512 + 16) + 8 * W;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};  // the attribute is per device
+    if (dev >= 64 || !attr_set[dev]) {
       KVDP_CUDA(cudaFuncSetAttribute(kvdp_hash_blocks_tma<8, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)smem));
-      attr_set = true;
+      if (dev < 64) attr_set[dev] = true;
     }
     const int64_t grid = std::min<int64_t>((warp_tiles + W - 1) / W, (int64_t)di.sm_count * 3);
     kvdp_hash_blocks_tma<8, W><<<(unsigned)std::max<int64_t>(grid, 1), W * 32, smem, stream>>>(A, S);
