@@ -22,6 +22,7 @@ KVDP_ENODEV = -19
 
 XFER_CHECK_DST_UNIQUE = 1
 HASH_TWIN_FIRST = 1
+HASH_NOALLOC_MAX_REQUESTS = 1 << 22
 IPC_HANDLE_BYTES = 64
 
 
@@ -108,6 +109,7 @@ PROTOTYPES = {
     "kvdp_host_tier_sync": (_i, [_vp]),
     "kvdp_hash_workspace_bytes": (_sz, [_i64]),
     "kvdp_hash_token_blocks": (_i, [_vp, _vp, _i64, _i64, _i32, _u64, _vp, _vp, _vp, _vp, _sz, _u32, _vp]),
+    "kvdp_hash_token_blocks_noalloc": (_i, [_vp, _vp, _i64, _i64, _i32, _u64, _vp, _vp, _vp, _u32, _vp]),
     "kvdp_hash_token_blocks_host": (_i, [_vp, _vp, _i64, _i32, _u64, _vp, _vp, _vp, _u32, _i32]),
     "kvdp_xxh3_64_batch": (_i, [_vp, _i64, _i64, _u64, _vp, _vp]),
 }

@@ -228,6 +228,22 @@ int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, i
                            int32_t block_size, uint64_t salt, int64_t* d_block_offsets, uint64_t* d_block_hash,
                            uint64_t* d_seq_hash, void* d_workspace, size_t workspace_bytes, uint32_t flags,
                            kvdp_stream_t stream);
+/* The same hashing for a caller that must not allocate device memory: a thread inside an engine whose memory manager
+ * took the whole GPU for the KV cache at start-up, or code where a cudaMalloc (which serialises the device) is not
+ * acceptable. It takes no workspace; the scan scratch lives in a 16 KiB __device__ array inside the library (held by
+ * every GPU that loads libkvdp.so, until exit). Limits and rules:
+ *   - at most KVDP_HASH_NOALLOC_MAX_REQUESTS requests per call; more returns KVDP_ERANGE and launches nothing;
+ *   - it calls no cudaMalloc / cudaFree / allocating routine; inputs and outputs are still the caller's buffers;
+ *   - the first call on each device looks up the scratch's device address (cudaGetSymbolAddress) and sets a kernel
+ *     attribute; make that first call outside any stream capture;
+ *   - all calls on one device share the one scratch: two calls whose kernels can overlap on the GPU (different
+ *     streams, no ordering between them) race on it. Calls ordered on one stream are fine; stale contents from the
+ *     previous call are never read.
+ * This entry point has no counterpart in the reference. */
+#define KVDP_HASH_NOALLOC_MAX_REQUESTS (1 << 22)
+int kvdp_hash_token_blocks_noalloc(const uint32_t* d_tokens, const int64_t* d_offsets, int64_t n_req,
+                                   int64_t total_tokens, int32_t block_size, uint64_t salt, int64_t* d_block_offsets,
+                                   uint64_t* d_block_hash, uint64_t* d_seq_hash, uint32_t flags, kvdp_stream_t stream);
 /* Host-buffer form (what a Rust caller of lib/tokens holds): uploads, hashes, downloads, synchronises.
  * h_block_offsets has n_req+1 entries; hash arrays must hold sum(len_r / block_size) entries. */
 int kvdp_hash_token_blocks_host(const uint32_t* h_tokens, const int64_t* h_offsets, int64_t n_req, int32_t block_size,
