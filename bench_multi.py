@@ -36,10 +36,11 @@ def run_multi(args, rank, local_rank, world):
 
     from dynamo_exp_b200 import _lib as lib
     L = lib.lib()
-    P = world // 2
-    D = world - P
-    is_prefill = rank < P
-    partner = (P + rank % D) if is_prefill else [r for r in range(P) if P + r % D == rank][0]
+    from dynamo_exp_b200.connector import split_roles
+    prefill_ranks, decode_ranks, role_pairs = split_roles(world)
+    P, D = len(prefill_ranks), len(decode_ranks)
+    is_prefill = rank in prefill_ranks
+    partner = dict(role_pairs)[rank] if is_prefill else [p for p, d in role_pairs if d == rank][0]
     pairs = BLOCKS_PER_REQ * args.requests
     n = args.cache_blocks
     steps, warmup = args.steps, args.warmup

@@ -46,6 +46,8 @@ class PlanDesc(C.Structure):
         ("dst_block_stride", C.c_int64),
         ("dst_row_stride", C.c_int64),
         ("dst_col_offset", C.c_int64),
+        ("src_row_stride", C.c_int64),
+        ("src_col_offset", C.c_int64),
         ("src_blocks", C.c_int64),
         ("dst_blocks", C.c_int64),
         ("src_layer_ptrs", C.c_void_p),
@@ -100,6 +102,7 @@ PROTOTYPES = {
     "kvdp_stream_wait_flag": (_i, [_vp, _vp, _u32]),
     "kvdp_peer_enable": (_i, [_i32, _i32]),
     "kvdp_ipc_export": (_i, [_vp, _vp]),
+    "kvdp_ipc_export_range": (_i, [_vp, _vp, C.POINTER(_u64)]),
     "kvdp_ipc_import": (_i, [_vp, _i32, _pp]),
     "kvdp_ipc_close": (_i, [_vp]),
     "kvdp_host_tier_create": (_i, [_pp, _vp, _i32, _i32, _i64, _i64, _vp, _i64, _i32, _i32]),

@@ -1,0 +1,411 @@
+"""KV transfer connector over libkvdp.so — the counterpart of the patched vLLM `DynamoNixlConnector`
+(container/deps/vllm/vllm_v0.8.4-dynamo-kv-disagg-patch.patch:1081-1492) with the same method surface:
+
+    register_kv_caches, get_agent_metadata, add_remote_agent, write_blocks, read_blocks, get_done_tranfers,
+    get_new_notifs, shutdown                                  (method names as in the reference, typo included)
+
+What changes underneath:
+  * no Triton rearrange pass and no staging blocks: the TP head reshard happens in the same kernel that moves the
+    bytes, so `staging_block_ids` is accepted and ignored, and block ids need not be contiguous (the reference
+    coalesces ranges, patch:1201-1294, only to cut its descriptor and launch counts);
+  * no NIXL/UCX: remote caches are CUDA-IPC peer mappings (or raw pointers when the "remote" agent lives in the same
+    process); WRITE = kernel on this GPU storing into the peer, READ = kernel on this GPU loading from the peer;
+  * decode TP smaller than prefill TP is supported (the reference asserts against it, patch:1437);
+  * notifications: after a write the sender drops `notify_msg` into a mailbox ring in the receiver's device memory
+    and bumps the ring head with a system-scope release store, all in stream order behind the data.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+
+import msgpack
+import numpy as np
+
+from . import _lib
+from .storage import KvError
+from .transfer import CopyPlan, TransferEngine
+
+MAILBOX_LANES = 64          # one lane per sender TP rank
+MAILBOX_SLOTS = 64          # ring depth per lane
+SLOT_BYTES = 128            # u32 len | u32 seq | 120 bytes of message
+HEADS_BYTES = MAILBOX_LANES * 64                       # one 64-byte line per lane head, all heads contiguous
+MAILBOX_BYTES = HEADS_BYTES + MAILBOX_LANES * MAILBOX_SLOTS * SLOT_BYTES
+MAX_MSG = SLOT_BYTES - 8
+
+
+def _head_off(lane: int) -> int:
+    return lane * 64
+
+
+def _slot_off(lane: int, slot: int) -> int:
+    return HEADS_BYTES + (lane * MAILBOX_SLOTS + slot) * SLOT_BYTES
+
+
+@dataclass
+class KvdpMetadata:
+    """What one engine publishes for its peers (the reference's `NixlMetadata`, patch:1081-1089; stored in etcd by
+    examples/llm/utils/nixl.py:59-116). `agent_metadata[rank]` is opaque bytes produced by `get_agent_metadata()`."""
+    engine_id: str
+    agent_metadata: List[bytes]
+    kv_caches_base_addr: List[List[List[int]]]   # [rank][layer][K, V] (informational; peers use the IPC handles)
+    num_blocks: int
+
+    def encode(self) -> bytes:
+        return msgpack.packb({"engine_id": self.engine_id, "agent_metadata": self.agent_metadata,
+                              "kv_caches_base_addr": self.kv_caches_base_addr, "num_blocks": self.num_blocks},
+                             use_bin_type=True)
+
+    @staticmethod
+    def decode(raw: bytes) -> "KvdpMetadata":
+        d = msgpack.unpackb(raw, raw=False)
+        return KvdpMetadata(d["engine_id"], list(d["agent_metadata"]), d["kv_caches_base_addr"], d["num_blocks"])
+
+
+def tp_targets(src_tp: int, dst_tp: int, src_rank: int) -> List[int]:
+    """Ranks of the other engine that rank `src_rank` exchanges blocks with (patch:1427-1471 for dst_tp >= src_tp:
+    `rank * tp_multiplier + i`; the dst_tp < src_tp direction is the inverse map)."""
+    if src_tp < 1 or dst_tp < 1 or not (0 <= src_rank < src_tp):
+        raise KvError("need src_tp, dst_tp >= 1 and 0 <= src_rank < src_tp")
+    if dst_tp >= src_tp:
+        if dst_tp % src_tp:
+            raise KvError("dst_tp must be a multiple of src_tp")
+        m = dst_tp // src_tp
+        return [src_rank * m + i for i in range(m)]
+    if src_tp % dst_tp:
+        raise KvError("src_tp must be a multiple of dst_tp")
+    return [src_rank // (src_tp // dst_tp)]
+
+
+def split_roles(world: int):
+    """Prefill:decode split used by the multi-GPU bench (north star: 2/4/8-GPU prefill:decode splits): the first
+    world // 2 ranks prefill, the rest decode; returns (prefill_ranks, decode_ranks, pairs) with prefill rank r paired
+    with decode rank P + r % D."""
+    if world < 2:
+        raise KvError("a prefill:decode split needs at least 2 ranks")
+    p = world // 2
+    d = world - p
+    prefill, decode = list(range(p)), list(range(p, world))
+    return prefill, decode, [(r, p + r % d) for r in prefill]
+
+
+@dataclass
+class _Remote:
+    tp: int
+    num_blocks: int
+    targets: List[int]
+    layer_ptrs: Dict[int, List[int]] = field(default_factory=dict)    # target rank -> per-layer base pointers
+    mailbox: Dict[int, int] = field(default_factory=dict)             # target rank -> mailbox base
+    mapped: List[int] = field(default_factory=list)                   # IPC mappings to close
+    push: Optional[CopyPlan] = None
+    pull: List[CopyPlan] = field(default_factory=list)
+    heads_per_rank: int = 0
+
+
+class DynamoKvdpConnector:
+    def __init__(self, engine_id: str, rank: int, tp_size: int, device: int = 0, is_mla: bool = False,
+                 max_blocks_per_transfer: int = 4096):
+        _lib.require_gpu()
+        self.engine_id = engine_id
+        self.rank = int(rank)
+        self.device = int(device)
+        self._tp_size = {engine_id: int(tp_size)}
+        self._is_mla = bool(is_mla)
+        self.num_layers = None
+        self.num_blocks = None
+        self.num_heads = None
+        self.block_len = None
+        self.block_size = None
+        self.kv_caches_base_addr: Dict[str, list] = {}
+        self._layer_ptrs: List[int] = []
+        self._remotes: Dict[str, _Remote] = {}
+        self._engine = TransferEngine(max_blocks_per_transfer, device)
+        L = _lib.lib()
+        p = C.c_void_p()
+        _lib.check(L.kvdp_device_alloc(C.byref(p), MAILBOX_BYTES, device))
+        self._mailbox = p.value
+        self._seen = [0] * MAILBOX_LANES
+        # sender-side: pinned message staging ring + a pinned progress word the stream bumps after each transfer
+        hp = C.c_void_p()
+        _lib.check(L.cuda_malloc_host(C.byref(hp), MAILBOX_SLOTS * SLOT_BYTES + 64))
+        self._host = hp.value
+        C.memset(self._host, 0, MAILBOX_SLOTS * SLOT_BYTES + 64)
+        self._progress = np.frombuffer((C.c_uint32 * 16).from_address(self._host + MAILBOX_SLOTS * SLOT_BYTES),
+                                       dtype=np.uint32)
+        self._send_seq: Dict[tuple, int] = {}     # (engine, target rank) -> messages sent on that lane
+        self._xfer_seq = 0
+        self._transfers: Dict[str, int] = {}      # notify_msg -> local sequence number
+
+    # ---------------------------------------------------------------------------------------------- registration
+    @property
+    def agent_name(self) -> str:
+        return f"{self.engine_id}:{self.rank}"
+
+    def register_kv_caches(self, kv_caches: Sequence, *, shape: Optional[Sequence[int]] = None,
+                           element_size: Optional[int] = None) -> None:
+        """`kv_caches`: one entry per layer — either a tensor-like with data_ptr()/shape/element_size() (vLLM layout
+        `[2, num_blocks, block_size, num_heads, head_dim]`; MLA `[num_blocks, block_size, head_dim]`, patch:1131-1186)
+        or a raw device pointer together with `shape` and `element_size`."""
+        if not kv_caches:
+            raise KvError("kv_caches must not be empty")
+        first = kv_caches[0]
+        if hasattr(first, "data_ptr"):
+            shape = tuple(first.shape)
+            element_size = first.element_size()
+            ptrs = [int(t.data_ptr()) for t in kv_caches]
+        else:
+            if shape is None or element_size is None:
+                raise KvError("raw pointers need shape and element_size")
+            ptrs = [int(p) for p in kv_caches]
+        if self._is_mla:
+            num_blocks, block_size, head_dim = shape
+            self.num_heads, self.num_cache_entries = 1, 1
+            self.block_len = head_dim * block_size * element_size
+        else:
+            two, num_blocks, block_size, num_heads, head_dim = shape
+            if two != 2:
+                raise KvError("expected a [2, num_blocks, block_size, num_heads, head_dim] cache per layer")
+            self.num_heads, self.num_cache_entries = num_heads, 2
+            self.block_len = block_size * num_heads * head_dim * element_size
+        self.block_size = block_size
+        self.num_layers = len(ptrs)
+        self.num_blocks = num_blocks
+        self._layer_ptrs = ptrs
+        self.kv_caches_base_addr[self.engine_id] = [
+            [p] if self._is_mla else [p, p + num_blocks * self.block_len] for p in ptrs]
+
+    def get_agent_metadata(self) -> bytes:
+        """Opaque per-rank blob: IPC handles (+ offsets) of every layer and of the mailbox, raw pointers for same-process
+        peers, and the geometry the peer needs to validate."""
+        if not self._layer_ptrs:
+            raise KvError("register_kv_caches must be called first")
+        L = _lib.lib()
+
+        def export(ptr):
+            h = (C.c_uint8 * _lib.IPC_HANDLE_BYTES)()
+            off = C.c_uint64(0)
+            _lib.check(L.kvdp_ipc_export_range(C.c_void_p(ptr), h, C.byref(off)))
+            return [bytes(h), int(off.value)]
+        return msgpack.packb({
+            "pid": os.getpid(), "rank": self.rank, "device": self.device, "tp": self._tp_size[self.engine_id],
+            "num_layers": self.num_layers, "num_blocks": self.num_blocks, "block_len": self.block_len,
+            "block_size": self.block_size, "is_mla": self._is_mla,
+            "layers": [export(p) for p in self._layer_ptrs], "layer_ptrs": self._layer_ptrs,
+            "mailbox": export(self._mailbox), "mailbox_ptr": self._mailbox}, use_bin_type=True)
+
+    def add_remote_agent(self, engine_id: str, agent_metadata: List[bytes], agent_tp: int,
+                         kv_caches_base_addr=None, num_blocks: Optional[int] = None) -> List[str]:
+        """reference: patch:1427-1471. Opens the peer caches this rank talks to and builds the push / pull plans."""
+        if not self._layer_ptrs:
+            raise KvError("register_kv_caches must be called first")
+        my_tp = self._tp_size[self.engine_id]
+        self._tp_size[engine_id] = int(agent_tp)
+        if len(agent_metadata) != agent_tp:
+            raise KvError(f"expected {agent_tp} agent metadata blobs, got {len(agent_metadata)}")
+        targets = tp_targets(my_tp, agent_tp, self.rank)
+        metas = [msgpack.unpackb(m, raw=False) for m in agent_metadata]
+        rem = _Remote(tp=int(agent_tp), num_blocks=int(num_blocks if num_blocks is not None else
+                                                       metas[targets[0]]["num_blocks"]), targets=targets)
+        L = _lib.lib()
+
+        def open_ptr(meta, handle_off, raw_ptr):
+            if meta["pid"] == os.getpid():
+                return int(raw_ptr)           # same process: the pointer is directly usable (peer access permitting)
+            hb = (C.c_uint8 * _lib.IPC_HANDLE_BYTES).from_buffer_copy(handle_off[0])
+            p = C.c_void_p()
+            _lib.check(L.kvdp_ipc_import(hb, self.device, C.byref(p)))
+            rem.mapped.append(p.value)
+            return p.value + int(handle_off[1])
+
+        for q in targets:
+            m = metas[q]
+            if m["num_layers"] != self.num_layers or m["block_size"] != self.block_size or m["is_mla"] != self._is_mla:
+                raise KvError("remote cache geometry does not match the local one")
+            if m["pid"] == os.getpid() and m["device"] != self.device:
+                _lib.check(L.kvdp_peer_enable(self.device, m["device"]))
+            rem.layer_ptrs[q] = [open_ptr(m, h, raw) for h, raw in zip(m["layers"], m["layer_ptrs"])]
+            rem.mailbox[q] = open_ptr(m, m["mailbox"], m["mailbox_ptr"])
+        self.kv_caches_base_addr[engine_id] = kv_caches_base_addr
+        self._remotes[engine_id] = rem
+        self._build_plans(engine_id, rem, metas)
+        return [f"{engine_id}:{q}" for q in targets]
+
+    def _build_plans(self, engine_id: str, rem: _Remote, metas) -> None:
+        my_tp = self._tp_size[self.engine_id]
+        if self._is_mla:
+            # latent cache: whole blocks, replicated to every target rank (patch:1440-1441,1451)
+            suffix = self.block_len
+            rem.push = None
+            rem.pull = []
+            rem._mla_push = [CopyPlan.block_copy_raw(self._layer_ptrs, rem.layer_ptrs[q], 1, self.num_blocks,
+                                                     rem.num_blocks, suffix, 1, self.device) for q in rem.targets]
+            rem.pull = [CopyPlan.block_copy_raw(rem.layer_ptrs[rem.targets[0]], self._layer_ptrs, 1, rem.num_blocks,
+                                                self.num_blocks, suffix, 1, self.device)]
+            return
+        row_bytes = self.block_len // self.block_size                      # heads_here * head_dim * elem
+        remote_row = metas[rem.targets[0]]["block_len"] // self.block_size
+        if row_bytes * my_tp != remote_row * rem.tp:
+            raise KvError("local and remote caches disagree on the model's total KV row size")
+        rem.push = CopyPlan.reshard(self._layer_ptrs, [rem.layer_ptrs[q] for q in rem.targets], self.num_blocks,
+                                    rem.num_blocks, self.block_size, row_bytes, my_tp, rem.tp, self.rank, self.device)
+        # pull = the remote ranks' reshard toward this rank, executed here with the remote caches as the source
+        rem.pull = [CopyPlan.reshard(rem.layer_ptrs[q], [self._layer_ptrs], rem.num_blocks, self.num_blocks,
+                                     self.block_size, remote_row, rem.tp, my_tp, q, self.device)
+                    for q in rem.targets] if rem.tp >= my_tp else [
+            # remote TP smaller than ours: one remote rank holds a superset of our heads; take our sub-rows
+            self._sub_row_pull_plan(rem, remote_row, row_bytes)]
+
+    def _sub_row_pull_plan(self, rem: _Remote, remote_row: int, row_bytes: int) -> CopyPlan:
+        """Remote TP smaller than ours: rank q = rank // m holds rows m times wider; read only our column range
+        [j*row_bytes, (j+1)*row_bytes), j = rank % m, of every remote token row (strided source rows)."""
+        q = rem.targets[0]
+        m = self._tp_size[self.engine_id] // rem.tp
+        j = self.rank % m
+        src = np.ascontiguousarray(rem.layer_ptrs[q], dtype=np.uint64)
+        dst = np.ascontiguousarray(self._layer_ptrs, dtype=np.uint64)
+        d = _lib.PlanDesc()
+        d.num_layers, d.row_groups, d.prefix_dim, d.rows = self.num_layers, 1, 2, self.block_size
+        d.run_bytes = row_bytes
+        d.src_prefix_stride = rem.num_blocks * self.block_size * remote_row
+        d.src_block_stride = self.block_size * remote_row
+        d.src_row_stride = remote_row
+        d.src_col_offset = j * row_bytes
+        d.dst_prefix_stride = self.num_blocks * self.block_len
+        d.dst_block_stride = self.block_len
+        d.dst_row_stride = row_bytes
+        d.dst_col_offset = 0
+        d.src_blocks, d.dst_blocks = rem.num_blocks, self.num_blocks
+        d.src_layer_ptrs = src.ctypes.data
+        d.dst_layer_ptrs = dst.ctypes.data
+        d.device = self.device
+        return CopyPlan.from_desc(d, keepalive=(src, dst))
+
+    # ---------------------------------------------------------------------------------------------- transfers
+    def write_blocks(self, local_block_ids, staging_block_ids, remote_block_ids, dst_engine_id: str,
+                     notify_msg: str) -> None:
+        """reference: patch:1361-1421. Asynchronous; completion is visible through get_done_tranfers() here and
+        get_new_notifs() on the receiver."""
+        rem = self._remote(dst_engine_id)
+        local_block_ids = list(local_block_ids)
+        remote_block_ids = list(remote_block_ids)[:len(local_block_ids)]   # patch:1368
+        if len(remote_block_ids) != len(local_block_ids):
+            raise KvError("fewer remote than local block ids")
+        if local_block_ids:
+            if self._is_mla:
+                for plan in rem._mla_push:
+                    self._engine.run(plan, local_block_ids, remote_block_ids, num_layers=self.num_layers)
+            else:
+                self._engine.run(rem.push, local_block_ids, remote_block_ids, num_layers=self.num_layers)
+        for q in rem.targets:                                              # empty => notify only (patch:1373-1377)
+            self._post(dst_engine_id, q, rem.mailbox[q], notify_msg)
+        self._xfer_seq += 1
+        self._transfers[notify_msg] = self._xfer_seq
+        self._engine.signal(self._host + MAILBOX_SLOTS * SLOT_BYTES, self._xfer_seq)
+
+    def read_blocks(self, local_block_ids, staging_block_ids, remote_block_ids, dst_engine_id: str) -> None:
+        """reference: patch:1296-1359. Blocking, like the reference (it polls the NIXL handles to DONE)."""
+        rem = self._remote(dst_engine_id)
+        local_block_ids, remote_block_ids = list(local_block_ids), list(remote_block_ids)
+        if len(local_block_ids) != len(remote_block_ids):
+            raise KvError("local and remote block id lists must have the same length")   # assert at patch:1299
+        if not local_block_ids:
+            return
+        if not rem.pull:
+            raise KvError("no pull plan for this peer")
+        for plan in rem.pull:
+            self._engine.run(plan, remote_block_ids, local_block_ids, num_layers=self.num_layers,
+                             check_dst_unique=True)
+        self._engine.sync()
+
+    def _post(self, engine_id: str, target_rank: int, mailbox_ptr: int, msg: str) -> None:
+        data = msg.encode("utf-8")
+        if len(data) > MAX_MSG:
+            raise KvError(f"notify message longer than {MAX_MSG} bytes")
+        key = (engine_id, target_rank)
+        seq = self._send_seq.get(key, 0) + 1
+        self._send_seq[key] = seq
+        slot = (seq - 1) % MAILBOX_SLOTS
+        # the pinned staging slot may still be in flight from MAILBOX_SLOTS messages ago
+        if seq > MAILBOX_SLOTS:
+            self._engine.sync()
+        rec = np.frombuffer((C.c_uint8 * SLOT_BYTES).from_address(self._host + slot * SLOT_BYTES), dtype=np.uint8)
+        rec[:] = 0
+        rec[:8].view(np.uint32)[:] = (len(data), seq)
+        rec[8:8 + len(data)] = np.frombuffer(data, dtype=np.uint8)
+        L = _lib.lib()
+        _lib.check(L.cuda_memcpy_async(C.c_void_p(mailbox_ptr + _slot_off(self.rank, slot)),
+                                       C.c_void_p(self._host + slot * SLOT_BYTES), SLOT_BYTES,
+                                       C.c_void_p(self._engine.stream)))
+        # release store of the lane head, ordered after data and message
+        self._engine.signal(mailbox_ptr + _head_off(self.rank), seq)
+
+    def get_done_tranfers(self) -> List[str]:
+        """Sender side: request ids whose transfer (data + notification) has completed (reference: patch:1473-1492)."""
+        done_upto = int(self._progress[0])
+        done = [m for m, s in self._transfers.items() if s <= done_upto]
+        for m in done:
+            del self._transfers[m]
+        return done
+
+    def get_new_notifs(self) -> Dict[str, List[str]]:
+        """Receiver side: messages that arrived since the last call, keyed by sender rank (reference: patch:1421-1425
+        returns NIXL's {agent_name: [notifs]})."""
+        L = _lib.lib()
+        out: Dict[str, List[str]] = {}
+        heads = np.zeros(HEADS_BYTES // 4, dtype=np.uint32)
+        _lib.check(L.cuda_memcpy_sync(C.c_void_p(heads.ctypes.data), C.c_void_p(self._mailbox), HEADS_BYTES))
+        lane_heads = heads[::16]
+        for lane in range(MAILBOX_LANES):
+            head = int(lane_heads[lane])
+            if head <= self._seen[lane]:
+                continue
+            msgs = []
+            first = max(self._seen[lane] + 1, head - MAILBOX_SLOTS + 1)
+            for seq in range(first, head + 1):
+                slot = (seq - 1) % MAILBOX_SLOTS
+                rec = np.zeros(SLOT_BYTES, dtype=np.uint8)
+                _lib.check(L.cuda_memcpy_sync(C.c_void_p(rec.ctypes.data),
+                                              C.c_void_p(self._mailbox + _slot_off(lane, slot)), SLOT_BYTES))
+                n, s = [int(x) for x in rec[:8].view(np.uint32)]
+                if s == seq:
+                    msgs.append(bytes(rec[8:8 + n]).decode("utf-8"))
+            self._seen[lane] = head
+            if msgs:
+                out[str(lane)] = msgs
+        return out
+
+    def sync(self) -> None:
+        self._engine.sync()
+
+    def _remote(self, engine_id: str) -> _Remote:
+        if engine_id not in self._remotes:
+            raise KvError(f"unknown remote engine {engine_id}: call add_remote_agent first")
+        return self._remotes[engine_id]
+
+    def shutdown(self) -> None:
+        """reference: patch:1188-1199."""
+        L = _lib.lib()
+        try:
+            self._engine.sync()
+        except Exception:
+            pass
+        for rem in self._remotes.values():
+            if rem.push:
+                rem.push.close()
+            for p in rem.pull:
+                p.close()
+            for p in getattr(rem, "_mla_push", []):
+                p.close()
+            for ptr in rem.mapped:
+                L.kvdp_ipc_close(C.c_void_p(ptr))
+        self._remotes.clear()
+        self._engine.close()
+        if self._mailbox:
+            L.kvdp_device_free(C.c_void_p(self._mailbox))
+            self._mailbox = 0
+        if self._host:
+            self._progress = None
+            L.cuda_free_host(C.c_void_p(self._host))
+            self._host = 0

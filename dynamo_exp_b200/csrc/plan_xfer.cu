@@ -140,6 +140,12 @@ int plan_build(kvdp_plan** out, const kvdp_plan_desc& d) {
   a.dst_block_stride = d.dst_block_stride;
   a.dst_row_stride = d.dst_row_stride;
   a.dst_col_offset = d.dst_col_offset;
+  a.src_row_stride = d.src_row_stride;
+  a.src_col_offset = d.src_col_offset;
+  if (d.src_row_stride < 0 || d.src_col_offset < 0 || (d.src_row_stride == 0 && d.src_col_offset != 0)) {
+    delete p;
+    return fail(KVDP_EINVAL, "plan: src_row_stride/src_col_offset must be >= 0 and used together");
+  }
   p->align = copy_alignment(a, p->h_src.data(), d.num_layers, p->h_dst.data(), n_dst);
 
   DeviceGuard g(p->device);

@@ -178,6 +178,28 @@ int kvdp_ipc_export(void* device_ptr, uint8_t handle[KVDP_IPC_HANDLE_BYTES]) {
   return 0;
 }
 
+int kvdp_ipc_export_range(void* device_ptr, uint8_t handle[KVDP_IPC_HANDLE_BYTES], uint64_t* offset) {
+  if (!device_ptr || !handle || !offset) return fail(KVDP_EINVAL, "kvdp_ipc_export_range: NULL argument");
+  typedef CUresult (*range_fn_t)(CUdeviceptr*, size_t*, CUdeviceptr);
+  static range_fn_t range_fn = nullptr;
+  if (!range_fn) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    KVDP_CUDA(cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q));
+    if (!fn || q != cudaDriverEntryPointSuccess) return fail(KVDP_ENODEV, "cuMemGetAddressRange is not available");
+    range_fn = (range_fn_t)fn;
+  }
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  CUresult r = range_fn(&base, &size, (CUdeviceptr)(uintptr_t)device_ptr);
+  if (r != CUDA_SUCCESS) return fail(KVDP_EINVAL, "cuMemGetAddressRange failed with CUresult %d", (int)r);
+  cudaIpcMemHandle_t h;
+  KVDP_CUDA(cudaIpcGetMemHandle(&h, (void*)(uintptr_t)base));
+  memcpy(handle, &h, sizeof h);
+  *offset = (uint64_t)((uintptr_t)device_ptr - (uintptr_t)base);
+  return 0;
+}
+
 int kvdp_ipc_import(const uint8_t handle[KVDP_IPC_HANDLE_BYTES], int32_t device, void** mapped_ptr) {
   if (!handle || !mapped_ptr) return fail(KVDP_EINVAL, "kvdp_ipc_import: NULL argument");
   cudaIpcMemHandle_t h;

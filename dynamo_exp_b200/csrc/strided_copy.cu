@@ -78,6 +78,15 @@ __device__ __forceinline__ char* dst_addr(const CopyArgs& a, const TileCoord& t,
   return (char*)(base + t.dst_chunk_rel + (uint64_t)r * (uint64_t)a.dst_row_stride + (uint64_t)a.dst_col_offset + x);
 }
 
+// source address of chunk byte offset `off` when source rows are strided (t.src then holds the chunk base + tile.off;
+// the tile offset is removed again here)
+__device__ __forceinline__ const char* src_addr_strided(const CopyArgs& a, const TileCoord& t, uint32_t off) {
+  const uint32_t rowlen = a.run_bytes * (uint32_t)a.row_groups;
+  const uint32_t r = off / rowlen;
+  const uint32_t x = off - r * rowlen;
+  return t.src - t.off + (uint64_t)r * (uint64_t)a.src_row_stride + (uint64_t)a.src_col_offset + x;
+}
+
 __device__ __forceinline__ void publish_done(const CopyArgs& a) {
   if (a.done_flag == nullptr) return;
   __threadfence_system();
@@ -133,7 +142,7 @@ __device__ __forceinline__ void st_vec(char* p, const typename VecT<VEC>::T& v) 
 }
 
 // ------------------------------------------------------------------------------------------------ path 1
-template <int VEC, bool CONTIG>
+template <int VEC, bool CONTIG, bool SRC_STRIDED = false>
 __global__ void __launch_bounds__(kVecThreads) kvdp_copy_vec_kernel(const __grid_constant__ CopyArgs a) {
   using V = typename VecT<VEC>::T;
   for (int64_t tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
@@ -145,7 +154,8 @@ __global__ void __launch_bounds__(kVecThreads) kvdp_copy_vec_kernel(const __grid
 #pragma unroll
       for (int u = 0; u < kVecUnroll; ++u) {
         const uint32_t v = v0 + u * kVecThreads;
-        if (v < nvec) regs[u] = ld_vec<VEC>(t.src + (size_t)v * VEC);
+        if (v < nvec)
+          regs[u] = ld_vec<VEC>(SRC_STRIDED ? src_addr_strided(a, t, t.off + v * VEC) : t.src + (size_t)v * VEC);
       }
 #pragma unroll
       for (int u = 0; u < kVecUnroll; ++u) {
@@ -270,7 +280,9 @@ int set_smem(K kernel, size_t bytes) {
 
 template <int VEC>
 int launch_vec(const CopyArgs& a, bool contig, int grid, cudaStream_t stream) {
-  if (contig)
+  if (a.src_row_stride != 0)
+    kvdp_copy_vec_kernel<VEC, false, true><<<grid, kVecThreads, 0, stream>>>(a);
+  else if (contig)
     kvdp_copy_vec_kernel<VEC, true><<<grid, kVecThreads, 0, stream>>>(a);
   else
     kvdp_copy_vec_kernel<VEC, false><<<grid, kVecThreads, 0, stream>>>(a);
@@ -295,6 +307,8 @@ uint32_t copy_alignment(const CopyArgs& a, const uint64_t* h_src_ptrs, int n_src
   fold((uint64_t)a.dst_row_stride);
   fold((uint64_t)a.dst_col_offset);
   fold((uint64_t)a.dst_group_stride);
+  fold((uint64_t)a.src_row_stride);
+  fold((uint64_t)a.src_col_offset);
   return (uint32_t)m;
 }
 
@@ -314,7 +328,7 @@ int launch_strided_copy(CopyArgs a, uint32_t align, const CopyLaunchHints& hints
   const bool contig =
       a.row_groups == 1 && a.dst_col_offset == 0 && (a.rows == 1 || a.dst_row_stride == (int64_t)a.run_bytes);
   int path = (int)opt.copy_path;
-  if (align < 16 || hints.host_memory) path = 1;
+  if (align < 16 || hints.host_memory || a.src_row_stride != 0) path = 1;
   if (path == 0) path = contig ? 3 : 2;
   if (path == 3 && !contig) path = 2;
 

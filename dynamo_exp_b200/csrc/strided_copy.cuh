@@ -24,6 +24,9 @@ struct CopyArgs {
   uint32_t chunk_bytes;  // rows * row_groups * run_bytes  (< 4 GiB on the kernel path)
   int64_t src_prefix_stride, src_block_stride;
   int64_t dst_prefix_stride, dst_block_stride, dst_row_stride, dst_col_offset;
+  // strided source rows (only for pulling a column range out of wider remote rows): when src_row_stride != 0 the
+  // chunk's row r starts at chunk_base + r*src_row_stride + src_col_offset instead of r*row_groups*run_bytes
+  int64_t src_row_stride, src_col_offset;
   uint32_t tile_bytes;
   uint32_t tiles_per_chunk;
   int64_t total_tiles;

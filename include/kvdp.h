@@ -139,6 +139,9 @@ typedef struct kvdp_plan_desc {
   int64_t run_bytes;
   int64_t src_prefix_stride, src_block_stride;
   int64_t dst_prefix_stride, dst_block_stride, dst_row_stride, dst_col_offset;
+  int64_t src_row_stride, src_col_offset; /* 0,0 = contiguous source chunk; else row r of the chunk is read from
+                                             chunk_base + r*src_row_stride + src_col_offset (a column range of wider
+                                             rows, e.g. pulling this rank's heads out of a smaller-TP peer's cache) */
   int64_t src_blocks, dst_blocks;    /* extents of the block axes, used to bounds-check ids (0 = unchecked) */
   const uint64_t* src_layer_ptrs;    /* host array [num_layers] */
   const uint64_t* dst_layer_ptrs;    /* host array [row_groups][num_layers] */
@@ -197,6 +200,9 @@ int kvdp_stream_wait_flag(kvdp_stream_t stream, uint32_t* flag, uint32_t value);
 #define KVDP_IPC_HANDLE_BYTES 64
 int kvdp_peer_enable(int32_t device, int32_t peer_device);            /* same-process peers */
 int kvdp_ipc_export(void* device_ptr, uint8_t handle[KVDP_IPC_HANDLE_BYTES]); /* ptr must be a kvdp_device_alloc base */
+/* Same for a pointer INSIDE a larger allocation (e.g. a tensor carved out of a framework's caching allocator): the
+ * handle names the whole allocation and *offset is device_ptr's distance from its base; the importer adds it back. */
+int kvdp_ipc_export_range(void* device_ptr, uint8_t handle[KVDP_IPC_HANDLE_BYTES], uint64_t* offset);
 int kvdp_ipc_import(const uint8_t handle[KVDP_IPC_HANDLE_BYTES], int32_t device, void** mapped_ptr);
 int kvdp_ipc_close(void* mapped_ptr);
 

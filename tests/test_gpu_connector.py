@@ -1,0 +1,164 @@
+"""GPU: the transfer connector (mirror of the patched vLLM DynamoNixlConnector, patch:1081-1492) — write_blocks (push),
+read_blocks (pull), TP resharding in both directions, notifications, MLA replication. All engine ranks live on ONE GPU in
+this process (ranks are separate cache slabs), so peers are reached through raw pointers; the cross-process CUDA-IPC
+path is covered by test_two_process_ipc_transfer below. Oracle: the formula-independent canonical-slice property
+ — every decode rank's cache equals the head slice of a TP1 cache at the mapped block ids."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from dynamo_exp_b200.connector import DynamoKvdpConnector, KvdpMetadata, tp_targets
+from dynamo_exp_b200.storage import KvError
+from tests.util import DevBuf
+
+pytestmark = pytest.mark.gpu
+
+L, H, D, BS, E = 3, 8, 16, 8, 2
+NP, ND = 9, 11
+
+
+def make_engine(gpu, engine_id, tp, num_blocks, canon=None):
+    """One connector + cache slabs per TP rank. If `canon` ([L,2,N,BS,H,D]) is given the caches hold its head slices."""
+    h = H // tp
+    conns, bufs = [], []
+    for r in range(tp):
+        layers = []
+        for l in range(L):
+            b = DevBuf(gpu, 2 * num_blocks * BS * h * D * E)
+            if canon is not None:
+                b.upload(np.ascontiguousarray(canon[l][:, :, :, r * h:(r + 1) * h, :]))
+            layers.append(b)
+        c = DynamoKvdpConnector(engine_id, r, tp, device=0)
+        c.register_kv_caches([b.ptr for b in layers], shape=(2, num_blocks, BS, h, D), element_size=E)
+        conns.append(c)
+        bufs.append(layers)
+    meta = KvdpMetadata(engine_id, [c.get_agent_metadata() for c in conns],
+                        [c.kv_caches_base_addr[engine_id] for c in conns], num_blocks)
+    return conns, bufs, KvdpMetadata.decode(meta.encode())     # through the wire format, like etcd would
+
+
+def read_rank(bufs, r, tp, num_blocks):
+    h = H // tp
+    return [b.download(np.int16).reshape(2, num_blocks, BS, h, D) for b in bufs[r]]
+
+
+@pytest.mark.parametrize("ptp,dtp", [(1, 1), (1, 2), (2, 4), (1, 4), (4, 2), (2, 1), (4, 1), (2, 2)])
+def test_write_blocks_reshards_and_notifies(gpu, ptp, dtp):
+    rng = np.random.Generator(np.random.PCG64(ptp * 10 + dtp))
+    canon = rng.integers(0, 2 ** 15, size=(L, 2, NP, BS, H, D), dtype=np.int16)
+    pre, pre_bufs, pre_meta = make_engine(gpu, "prefill", ptp, NP, canon)
+    dec, dec_bufs, dec_meta = make_engine(gpu, "decode", dtp, ND)
+    local, remote = [7, 0, 3, 5], [2, 10, 0, 6, 9]          # one extra remote id: truncated like patch:1368
+    for c in pre:
+        names = c.add_remote_agent("decode", dec_meta.agent_metadata, dtp, dec_meta.kv_caches_base_addr,
+                                   dec_meta.num_blocks)
+        assert names == [f"decode:{q}" for q in tp_targets(ptp, dtp, c.rank)]
+        c.write_blocks(local, [0] * len(local), remote, "decode", f"req-42-from-{c.rank}")
+    for c in pre:
+        c.sync()
+        assert c.get_done_tranfers() == [f"req-42-from-{c.rank}"]
+        assert c.get_done_tranfers() == []
+    hq = H // dtp
+    for q in range(dtp):
+        got = read_rank(dec_bufs, q, dtp, ND)
+        for l in range(L):
+            want = canon[l][:, local][:, :, :, q * hq:(q + 1) * hq, :]
+            assert np.array_equal(got[l][:, remote[:4]], want), (q, l)
+        senders = sorted(p for p in range(ptp) if q in tp_targets(ptp, dtp, p))
+        notifs = dec[q].get_new_notifs()
+        assert notifs == {str(p): [f"req-42-from-{p}"] for p in senders}
+        assert dec[q].get_new_notifs() == {}
+    # empty transfer: notify only (patch:1373-1377)
+    pre[0].write_blocks([], [], [1, 2], "decode", "empty")
+    pre[0].sync()
+    for q in tp_targets(ptp, dtp, 0):
+        assert dec[q].get_new_notifs() == {"0": ["empty"]}
+    for c in pre + dec:
+        c.shutdown()
+
+
+@pytest.mark.parametrize("ptp,dtp", [(1, 1), (1, 2), (2, 4), (4, 2), (2, 1), (4, 1)])
+def test_read_blocks_pulls_and_inverts_the_reshard(gpu, ptp, dtp):
+    """read_blocks (patch:1296-1359): the prefill side pulls prefix-hit blocks out of the decode caches. Any TP ratio,
+    including decode TP < prefill TP (strided source rows), which the reference cannot do."""
+    rng = np.random.Generator(np.random.PCG64(ptp * 7 + dtp))
+    canon = rng.integers(0, 2 ** 15, size=(L, 2, ND, BS, H, D), dtype=np.int16)
+    dec, dec_bufs, dec_meta = make_engine(gpu, "decode", dtp, ND, canon)
+    pre, pre_bufs, pre_meta = make_engine(gpu, "prefill", ptp, NP)
+    remote, local = [10, 1, 4], [0, 8, 3]
+    hp = H // ptp
+    for c in pre:
+        c.add_remote_agent("decode", dec_meta.agent_metadata, dtp, dec_meta.kv_caches_base_addr, dec_meta.num_blocks)
+        c.read_blocks(local, local, remote, "decode")        # blocking
+        got = read_rank(pre_bufs, c.rank, ptp, NP)
+        for l in range(L):
+            want = canon[l][:, remote][:, :, :, c.rank * hp:(c.rank + 1) * hp, :]
+            assert np.array_equal(got[l][:, local], want), (c.rank, l)
+    with pytest.raises(KvError):
+        pre[0].read_blocks([0], [0], [1, 2], "decode")
+    with pytest.raises(KvError, match="unknown remote engine"):
+        pre[0].write_blocks([0], [0], [0], "nobody", "x")
+    for c in pre + dec:
+        c.shutdown()
+
+
+def test_mla_latent_cache_is_replicated(gpu):
+    """MLA branch (patch:1138-1160, 1440-1451): one [num_blocks, block_size, head_dim] entry per layer, no head split;
+    every target rank receives the full block."""
+    nb, bs, hd = 6, 4, 24
+    rng = np.random.Generator(np.random.PCG64(5))
+    src_h = [rng.integers(0, 255, size=(nb, bs, hd), dtype=np.uint8) for _ in range(L)]
+    src = [DevBuf(gpu, a.nbytes) for a in src_h]
+    for b, a in zip(src, src_h):
+        b.upload(a)
+    pre = DynamoKvdpConnector("p", 0, 1, device=0, is_mla=True)
+    pre.register_kv_caches([b.ptr for b in src], shape=(nb, bs, hd), element_size=1)
+    decs, dbufs = [], []
+    for r in range(2):
+        bufs = [DevBuf(gpu, nb * bs * hd) for _ in range(L)]
+        c = DynamoKvdpConnector("d", r, 2, device=0, is_mla=True)
+        c.register_kv_caches([b.ptr for b in bufs], shape=(nb, bs, hd), element_size=1)
+        decs.append(c)
+        dbufs.append(bufs)
+    pre.add_remote_agent("d", [c.get_agent_metadata() for c in decs], 2, None, nb)
+    pre.write_blocks([5, 1], [0, 0], [0, 3], "d", "mla")
+    pre.sync()
+    for r in range(2):
+        for l in range(L):
+            got = dbufs[r][l].download().reshape(nb, bs, hd)
+            assert np.array_equal(got[[0, 3]], src_h[l][[5, 1]])
+        assert decs[r].get_new_notifs() == {"0": ["mla"]}
+    for c in [pre] + decs:
+        c.shutdown()
+
+
+def test_many_notifications_wrap_the_mailbox_ring(gpu):
+    dec, dec_bufs, dec_meta = make_engine(gpu, "decode", 1, ND)      # keep the cache slabs alive
+    pre, pre_bufs, _ = make_engine(gpu, "prefill", 1, NP)
+    pre[0].add_remote_agent("decode", dec_meta.agent_metadata, 1, None, ND)
+    sent = []
+    for k in range(150):                      # ring depth is 64: drain in between like a polling decode worker
+        pre[0].write_blocks([k % NP], [0], [k % ND], "decode", f"r{k}")
+        sent.append(f"r{k}")
+        if k % 40 == 39:
+            pre[0].sync()
+            got = dec[0].get_new_notifs().get("0", [])
+            assert got == sent[:len(got)]
+            sent = sent[len(got):]
+    pre[0].sync()
+    assert dec[0].get_new_notifs().get("0", []) == sent
+    for c in pre + dec:
+        c.shutdown()
+    del dec_bufs, pre_bufs
+
+
+def test_two_process_ipc_transfer(gpu):
+    """Two OS processes on the same GPU exchange metadata through a file and move blocks through CUDA-IPC mappings
+    (the path the multi-GPU bench uses across GPUs). Host-side polling only: no kernel waits on another process."""
+    script = os.path.join(os.path.dirname(__file__), "mp_connector_check.py")
+    r = subprocess.run([sys.executable, script], capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "IPC OK" in r.stdout
