@@ -88,20 +88,21 @@ def run_multi(args, rank, local_rank, world):
     dist.barrier()
     seq = {"v": 0}
 
-    def timed(mode, k0, count):
+    def timed(mode, k0, count, su=None):
         """Barrier + device sync on both sides, CUDA events on the launching stream, MAX over ranks. The passive side
         stream-waits on the completion flag the kernel's last CTA writes into its memory."""
+        su = su or setup
         runner = is_prefill if mode == "push" else not is_prefill
         torch.cuda.synchronize()
         dist.barrier()
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        st = setup.stream if runner else wait_stream
+        st = su.stream if runner else wait_stream
         a.record(st)
         if runner:
             for k in range(count):
                 seq["v"] += 1
-                setup.step(k0 + k, done_flag=peer_flag, done_value=seq["v"])
+                su.step(k0 + k, done_flag=peer_flag, done_value=seq["v"])
         else:
             seq["v"] += count
             lib.check(L.kvdp_stream_wait_flag(C.c_void_p(wait_stream.cuda_stream), flag_ptr, seq["v"]))
@@ -159,6 +160,37 @@ def run_multi(args, rank, local_rank, world):
         verify(mode, warmup + steps - 1)
         results[mode] = {"value": P * pairs * BLOCK_BYTES * steps / sec / GB, "sec": sec,
                          "per_direction": pairs * BLOCK_BYTES * steps / sec / GB * max(1, P // D)}
+
+    # ---- e2e: source blocks in pinned HOST memory on the prefill side, ONE kernel reads them over PCIe and stores
+    # them into the decode GPU's cache over NVLink (no bounce through prefill HBM); decode reads back 8 bytes.
+    e2e = None
+    if not args.no_e2e:
+        import copy
+        nh = 128                                      # 1 GiB of pinned blocks per prefill rank
+        e_args = copy.copy(args)
+        e_args.cache_blocks, e_args.requests = nh, nh // BLOCKS_PER_REQ
+        host_ptrs, e_setup = [], None
+        if is_prefill:
+            for l in range(L8B):
+                p = C.c_void_p()
+                lib.check(L.cuda_malloc_host(C.byref(p), 2 * nh * CHUNK))
+                a = np.frombuffer((C.c_uint8 * (2 * nh * CHUNK)).from_address(p.value), dtype=np.uint8)
+                a[:] = (l * 11 + rank) & 0xFF
+                host_ptrs.append(p.value)
+            e_setup = Setup(e_args, torch, lib, device=local_rank, dst_contig_ptr=peer_cache.value, dst_blocks=n,
+                            src_ptrs=host_ptrs)
+        k_e = max(2, min(steps, 5))
+        timed("push", 0, 1, e_setup)
+        sec_e = timed("push", 1, k_e, e_setup)
+        result = np.zeros(8, dtype=np.uint8)
+        if not is_prefill:
+            lib.check(L.cuda_memcpy_sync(result.ctypes.data, own_cache, 8))
+        e2e = {"value": P * nh * BLOCK_BYTES * k_e / sec_e / GB, "unit": "GB/s",
+               "h2d_bytes_per_step": P * nh * BLOCK_BYTES, "d2h_bytes_per_step": 8 * D, "steps": k_e,
+               "api": "kvdp_plan_contig over pinned host layer pointers -> peer-mapped decode cache, kvdp_xfer_run with "
+                      "in-kernel completion flag; one launch per step, PCIe-bound per prefill GPU"}
+        for p in host_ptrs:
+            L.cuda_free_host(C.c_void_p(p))
 
     # ---- comparators: (i) local relayout into HBM staging + NCCL send/recv, (ii) plain peer memcpy of the payload
     nccl_value = memcpy_value = None
@@ -239,8 +271,7 @@ def run_multi(args, rank, local_rank, world):
                             "steps": nsteps_c},
             "options": {k: lib.get_option(k) for k in ("copy_path", "tile_bytes", "stages", "ctas_per_sm")},
             "gpu_launches": steps * len(modes), "clocks": clk,
-            "e2e": {"value": None, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
-                    "note": "see the N=1 line: the host-buffer path is PCIe-bound per GPU and does not cross NVLink"},
+            "e2e": e2e,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()

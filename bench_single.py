@@ -195,6 +195,75 @@ def e2e_legacy(torch, lib, args, steps, warmup):
                    "(pinned host layer-separate blocks -> HBM), timed on the host clock around the blocking call"}
 
 
+def host_tier_bench(torch, lib):
+    """BASELINE config 4: offload / onboard of Llama-3-8B blocks between HBM (layer-separate) and a pinned
+    contiguous-per-block host slab, mixed ISL 1k..32k (16..512 blocks per request), through kvdp_host_tier_*."""
+    L = lib.lib()
+    isl_blocks = [16, 32, 64, 128, 256, 16]           # 1k, 2k, 4k, 8k, 16k (+1k) = 512 blocks = 4 GiB
+    nb = sum(isl_blocks)
+    dev_layers = [torch.empty(2 * nb * CHUNK, dtype=torch.uint8, device="cuda").random_(0, 256) for _ in range(L8B)]
+    back_layers = [torch.zeros(2 * nb * CHUNK, dtype=torch.uint8, device="cuda") for _ in range(L8B)]
+    host = C.c_void_p()
+    lib.check(L.cuda_malloc_host(C.byref(host), nb * BLOCK_BYTES))
+    ptrs = np.array([t.data_ptr() for t in dev_layers], dtype=np.uint64)
+    ptrs_b = np.array([t.data_ptr() for t in back_layers], dtype=np.uint64)
+    tier, tier_b = C.c_void_p(), C.c_void_p()
+    lib.check(L.kvdp_host_tier_create(C.byref(tier), ptrs.ctypes.data, L8B, 0, nb, CHUNK, host, nb, 32, 0))
+    lib.check(L.kvdp_host_tier_create(C.byref(tier_b), ptrs_b.ctypes.data, L8B, 0, nb, CHUNK, host, nb, 32, 0))
+    rng = np.random.Generator(np.random.PCG64(4))
+    dev_ids = rng.permutation(nb).astype(np.int32)      # scattered on the device
+    back_ids = rng.permutation(nb).astype(np.int32)
+    host_ids = np.arange(nb, dtype=np.int32)            # each request lands in a consecutive host range
+    reqs, o = [], 0
+    for n in isl_blocks:
+        reqs.append((o, n))
+        o += n
+
+    def run(t, fn, a_ids, b_ids):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for o, n in reqs:
+            lib.check(fn(t, a_ids[o:o + n].ctypes.data, b_ids[o:o + n].ctypes.data, n))
+        lib.check(L.kvdp_host_tier_sync(t))
+        return time.perf_counter() - t0
+    run(tier, L.kvdp_host_tier_offload, dev_ids, host_ids)                      # warm-up
+    t_off = min(run(tier, L.kvdp_host_tier_offload, dev_ids, host_ids) for _ in range(3))
+    run(tier_b, L.kvdp_host_tier_onboard, host_ids, back_ids)
+    t_on = min(run(tier_b, L.kvdp_host_tier_onboard, host_ids, back_ids) for _ in range(3))
+    # round trip identity on sampled blocks
+    for i in (0, 17, nb - 1):
+        for l in (0, 13, L8B - 1):
+            for kv in (0, 1):
+                a = dev_layers[l][(kv * nb + int(dev_ids[i])) * CHUNK:(kv * nb + int(dev_ids[i]) + 1) * CHUNK]
+                b = back_layers[l][(kv * nb + int(back_ids[i])) * CHUNK:(kv * nb + int(back_ids[i]) + 1) * CHUNK]
+                if not torch.equal(a, b):
+                    raise RuntimeError("host tier round trip mismatch")
+    # link ceilings: one contiguous 1 GiB DMA each way
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ceil = {}
+    for name, dst, src in (("d2h", host.value, dev_layers[0].data_ptr()), ("h2d", dev_layers[0].data_ptr(), host.value)):
+        best = 0.0
+        nbytes = min(1 << 30, 2 * nb * CHUNK)
+        for _ in range(3):
+            ev[0].record()
+            lib.check(L.cuda_memcpy_async(dst, src, nbytes, None))
+            ev[1].record()
+            torch.cuda.synchronize()
+            best = max(best, nbytes / (ev[0].elapsed_time(ev[1]) / 1e3) / GB)
+        ceil[name] = best
+    L.kvdp_host_tier_destroy(tier)
+    L.kvdp_host_tier_destroy(tier_b)
+    L.cuda_free_host(host)
+    payload = nb * BLOCK_BYTES
+    return {"workload": "Llama-3-8B blocks, requests of %s blocks (ISL 1k..16k mix), 4 GiB per direction" % isl_blocks,
+            "offload_GBps": payload / t_off / GB, "onboard_GBps": payload / t_on / GB,
+            "d2h_link_ceiling_GBps": ceil["d2h"], "h2d_link_ceiling_GBps": ceil["h2d"],
+            "offload_frac_of_ceiling": payload / t_off / GB / ceil["d2h"],
+            "onboard_frac_of_ceiling": payload / t_on / GB / ceil["h2d"],
+            "blocks_per_s_offload": nb / t_off, "blocks_per_s_onboard": nb / t_on,
+            "staging": "2 x 32 blocks (2 x 256 MiB HBM), one DMA per request range, gather/scatter kernel per slot"}
+
+
 def hash_bench(torch, lib, steps, warmup, peak):
     """Router-sweep shaped batch (ISL 512..32k round-robin, 64-token blocks) resident in HBM; chained + block hashes."""
     from tests.util import mix64
@@ -253,8 +322,25 @@ def hash_bench(torch, lib, steps, warmup, peak):
     ends[1].record(streams[1])
     torch.cuda.synchronize()
     sec = max(start.elapsed_time(ends[0]), start.elapsed_time(ends[1])) / 1e3 / n_pipe
+    # (3) router form: un-chained seed-1337 LocalBlockHash only (kv_router/indexer.rs:123-135), one stream
+    def run_unchained(salt):
+        st = streams[0]
+        boff, bh, sh, ws = outs[0]
+        lib.check(L.kvdp_hash_token_blocks(tok.data_ptr(), d_off.data_ptr(), n_req, total, BS, salt, boff.data_ptr(),
+                                           bh.data_ptr(), None, ws.data_ptr(), ws_bytes, 0,
+                                           C.c_void_p(st.cuda_stream)))
+    run_unchained(1337)
+    torch.cuda.synchronize()
+    a.record(streams[0])
+    for k in range(steps):
+        run_unchained(1337)
+    b.record(streams[0])
+    torch.cuda.synchronize()
+    sec_un = a.elapsed_time(b) / 1e3 / steps
     out = {"hashes_per_s": nblk / sec, "tokens_per_s": total / sec, "ms_per_batch": sec * 1e3, "requests": n_req,
            "blocks": nblk, "launches_per_batch": 3, "streams": 2,
+           "unchained_router_form": {"hashes_per_s": nblk / sec_un, "ms_per_batch": sec_un * 1e3,
+                                     "hbm_frac": nblk * 264 / sec_un / GB / peak},
            "single_stream": {"hashes_per_s": nblk / sec_serial, "ms_per_batch": sec_serial * 1e3},
            "roofline": {"bound": "hbm", "achieved": nblk * 272 / sec / GB, "peak": peak, "unit": "GB/s",
                         "frac": nblk * 272 / sec / GB / peak, "traffic": ncu_traffic("kvdp_hash_blocks_tma")}}
@@ -317,6 +403,9 @@ def run_single(args):
     torch.cuda.empty_cache()
     if not args.no_e2e:
         line["e2e"] = e2e_legacy(torch, lib, args, min(args.steps, 8), 2)
+    if not args.no_e2e:
+        line["host_tier"] = host_tier_bench(torch, lib)
+        torch.cuda.empty_cache()
     if not args.no_hash:
         line["hash"] = hash_bench(torch, lib, 10, 3, peak)
         line["hashes_per_s"] = line["hash"]["hashes_per_s"]
