@@ -79,6 +79,101 @@ def tp_targets(src_tp: int, dst_tp: int, src_rank: int) -> List[int]:
     return [src_rank // (src_tp // dst_tp)]
 
 
+def get_ranges(block_ids: Sequence[int]) -> List[List[int]]:
+    """Maximal runs of consecutive ids, `[0,1,2,4,5,6] -> [[0,2],[4,6]]` (reference: `_get_ranges`, patch:1201-1213).
+    The connector here does not need it (no staging, no per-range launches); kept for callers that mirror the
+    reference's bookkeeping and for the host tier's DMA coalescing."""
+    ranges: List[List[int]] = []
+    for i, b in enumerate(block_ids):
+        if i == 0 or b != block_ids[i - 1] + 1:
+            ranges.append([b, b])
+        else:
+            ranges[-1][1] = b
+    return ranges
+
+
+def get_same_length_ranges(src_ranges, dst_ranges):
+    """Split two range lists so that corresponding ranges have equal length (reference: `_get_same_length_ranges`,
+    patch:1247-1294; its example: src [[0,2],[4,8]], dst [[1,3],[5,7],[9,10]] ->
+    ([[0,2],[4,6],[7,8]], [[1,3],[5,7],[9,10]]))."""
+    src = [list(r) for r in src_ranges]
+    dst = [list(r) for r in dst_ranges]
+    out_s, out_d = [], []
+    i = j = 0
+    while i < len(src) and j < len(dst):
+        ls = src[i][1] - src[i][0] + 1
+        ld = dst[j][1] - dst[j][0] + 1
+        if ls == ld:
+            out_s.append([src[i][0], src[i][1]])
+            out_d.append([dst[j][0], dst[j][1]])
+            i += 1
+            j += 1
+        elif ls > ld:
+            out_s.append([src[i][0], src[i][0] + ld - 1])
+            out_d.append([dst[j][0], dst[j][1]])
+            src[i] = [src[i][0] + ld, src[i][1]]
+            j += 1
+        else:
+            out_s.append([src[i][0], src[i][1]])
+            out_d.append([dst[j][0], dst[j][0] + ls - 1])
+            dst[j] = [dst[j][0] + ls, dst[j][1]]
+            i += 1
+    return out_s, out_d
+
+
+def rearrange_tensors(t1_ptr: int, t2_ptr: int, shape: Sequence[int], element_size: int, d: int, direction: str,
+                      device: int = -1, engine: Optional[TransferEngine] = None) -> None:
+    """Device counterpart of the reference's Triton `rearrange_tensors(t1, t2, d, direction)` (patch:934-1031) for one
+    K-or-V tensor of shape [N, B, H, C]:
+        write: t2 viewed as [d][N][B][H/d][C]  <-  t1[n][b][g*H/d + h'][c]
+        read : t1  <-  t2 (the inverse)
+    The transfer connector never calls it (the reshard is fused into the transfer); it exists so that code written
+    against the reference's two-step scheme keeps working, and as a directly testable statement of the index map.
+    Unlike the Triton kernels it needs no `N*B*H*C % 1024 == 0`."""
+    N, B, H, Cc = [int(x) for x in shape]
+    if d < 1 or H % d:
+        raise KvError("H must be divisible by d")
+    if direction not in ("read", "write"):
+        raise KvError(f"Invalid direction: {direction}")
+    run = (H // d) * Cc * element_size
+    row = H * Cc * element_size
+    own = engine is None
+    eng = engine or TransferEngine(max(N, 1), device)
+    ids = list(range(N))
+    plans = []
+    try:
+        if direction == "write":
+            desc = _lib.PlanDesc()
+            src = np.array([t1_ptr], dtype=np.uint64)
+            dst = np.array([t2_ptr + g * N * B * run for g in range(d)], dtype=np.uint64)
+            desc.num_layers, desc.row_groups, desc.prefix_dim, desc.rows = 1, d, 1, B
+            desc.run_bytes = run
+            desc.src_block_stride, desc.dst_block_stride, desc.dst_row_stride = B * row, B * run, run
+            desc.src_blocks = desc.dst_blocks = N
+            desc.src_layer_ptrs, desc.dst_layer_ptrs, desc.device = src.ctypes.data, dst.ctypes.data, device
+            plans.append(CopyPlan.from_desc(desc, keepalive=(src, dst)))
+        else:
+            for g in range(d):   # group g of the staging layout lands in column range g of every t1 row
+                desc = _lib.PlanDesc()
+                src = np.array([t2_ptr + g * N * B * run], dtype=np.uint64)
+                dst = np.array([t1_ptr], dtype=np.uint64)
+                desc.num_layers, desc.row_groups, desc.prefix_dim, desc.rows = 1, 1, 1, B
+                desc.run_bytes = run
+                desc.src_block_stride, desc.dst_block_stride = B * run, B * row
+                desc.dst_row_stride, desc.dst_col_offset = row, g * run
+                desc.src_blocks = desc.dst_blocks = N
+                desc.src_layer_ptrs, desc.dst_layer_ptrs, desc.device = src.ctypes.data, dst.ctypes.data, device
+                plans.append(CopyPlan.from_desc(desc, keepalive=(src, dst)))
+        for p in plans:
+            eng.run(p, ids, ids, num_layers=1)
+        eng.sync()
+    finally:
+        for p in plans:
+            p.close()
+        if own:
+            eng.close()
+
+
 def split_roles(world: int):
     """Prefill:decode split used by the multi-GPU bench (north star: 2/4/8-GPU prefill:decode splits): the first
     world // 2 ranks prefill, the rest decode; returns (prefill_ranks, decode_ranks, pairs) with prefill rank r paired

@@ -384,7 +384,10 @@ __device__ __forceinline__ int64_t req_blocks(const int64_t* __restrict__ offset
                                               int32_t bs) {
   if (r >= n_req) return 0;
   const int64_t len = __ldg(offsets + r + 1) - __ldg(offsets + r);
-  return len > 0 ? len / bs : 0;
+  if (len <= 0) return 0;
+  // request lengths almost always fit 32 bits: a 32-bit divide is ~5x cheaper than the 64-bit one
+  if (len <= 0xffffffffLL) return (int64_t)((uint32_t)len / (uint32_t)bs);
+  return len / bs;
 }
 
 __device__ __forceinline__ int64_t block_exclusive_scan(int64_t v, int64_t* total, int64_t* warp_sums) {

@@ -94,6 +94,31 @@ def compute_block_hash_for_seq(tokens, kv_block_size: int) -> List[int]:
     return [int(x) for x in bh]
 
 
+def kv_event_create_stored_from_parts(event_id: int, token_ids, num_block_tokens, block_ids, kv_block_size: int,
+                                      parent_hash: Optional[int] = None, lora_id: int = 0) -> dict:
+    """The hashing half of the engine-facing `dynamo_kv_event_publish_stored` (lib/bindings/c/src/lib.rs:157-227,
+    260-295): one stored-blocks event from parts. Blocks are taken in order until the first one whose token count is
+    not `kv_block_size` (the reference stops the batch there, :191-210); each published block carries the engine's
+    block id as `block_hash` and the seed-1337 un-chained token hash as `tokens_hash`. All kept blocks are hashed in ONE
+    GPU batch instead of one call per block. (Publishing to NATS is out of scope; this returns the event payload.)"""
+    tok = _as_u32(token_ids)
+    counts = [int(x) for x in num_block_tokens]
+    ids = [int(x) for x in block_ids]
+    if len(counts) != len(ids):
+        raise KvError("num_block_tokens and block_ids must have the same length")
+    keep = 0
+    for n in counts:
+        if n != kv_block_size:
+            break
+        keep += 1
+    if keep * kv_block_size > tok.size:
+        raise KvError("token_ids is shorter than the blocks it is said to hold")
+    hashes = compute_block_hash_for_seq(tok[:keep * kv_block_size], kv_block_size) if keep else []
+    return {"event_id": int(event_id),
+            "data": {"stored": {"parent_hash": None if parent_hash is None else int(parent_hash),
+                                "blocks": [{"block_hash": ids[i], "tokens_hash": hashes[i]} for i in range(keep)]}}}
+
+
 class Tokens:
     """reference: lib/tokens/src/lib.rs:48-128."""
 

@@ -84,3 +84,16 @@ def test_split_roles():
     assert split_roles(8)[2] == [(0, 4), (1, 5), (2, 6), (3, 7)]
     p, d, pairs = split_roles(6)
     assert (p, d) == ([0, 1, 2], [3, 4, 5])
+
+
+def test_range_helpers_match_the_reference_docstrings():
+    from dynamo_exp_b200.connector import get_ranges, get_same_length_ranges
+    # patch:1202-1203
+    assert get_ranges([0, 1, 2, 4, 5, 6]) == [[0, 2], [4, 6]]
+    assert get_ranges([]) == [] and get_ranges([7]) == [[7, 7]] and get_ranges([3, 2, 1]) == [[3, 3], [2, 2], [1, 1]]
+    # patch:1248-1250
+    assert get_same_length_ranges([[0, 2], [4, 8]], [[1, 3], [5, 7], [9, 10]]) == \
+        ([[0, 2], [4, 6], [7, 8]], [[1, 3], [5, 7], [9, 10]])
+    s, d = get_same_length_ranges([[0, 9]], [[0, 3], [10, 15]])
+    assert s == [[0, 3], [4, 9]] and d == [[0, 3], [10, 15]]
+    assert all(a[1] - a[0] == b[1] - b[0] for a, b in zip(s, d))

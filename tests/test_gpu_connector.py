@@ -162,3 +162,29 @@ def test_two_process_ipc_transfer(gpu):
     r = subprocess.run([sys.executable, script], capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "IPC OK" in r.stdout
+
+
+@pytest.mark.parametrize("d", [1, 2, 4])
+@pytest.mark.parametrize("shape,esz", [((3, 4, 8, 16), 2), ((5, 2, 4, 3), 4), ((2, 64, 8, 128), 2)])
+def test_rearrange_tensors_matches_the_triton_index_map(gpu, oracle, d, shape, esz):
+    """patch:934-1031; oracle = kvo_rearrange, itself pinned to reshape(N,B,d,H/d,C).transpose(2,0,1,3,4) on CPU."""
+    from dynamo_exp_b200.connector import rearrange_tensors
+    N, B, H, Cc = shape
+    dt = {2: np.int16, 4: np.int32}[esz]
+    rng = np.random.Generator(np.random.PCG64(d + N))
+    t1 = rng.integers(0, 2 ** 15, size=shape).astype(dt)
+    want = np.zeros_like(t1)
+    assert oracle.rearrange(t1, want, d, "write") == 0
+    d1, d2 = DevBuf(gpu, t1.nbytes), DevBuf(gpu, t1.nbytes)
+    d1.upload(t1)
+    rearrange_tensors(d1.ptr, d2.ptr, shape, esz, d, "write")
+    got = d2.download(dt).reshape(shape)
+    assert np.array_equal(got, want)
+    assert np.array_equal(got.reshape(d, N, B, H // d, Cc), t1.reshape(N, B, d, H // d, Cc).transpose(2, 0, 1, 3, 4))
+    back = DevBuf(gpu, t1.nbytes)
+    rearrange_tensors(back.ptr, d2.ptr, shape, esz, d, "read")
+    assert np.array_equal(back.download(dt).reshape(shape), t1)
+    with pytest.raises(KvError):
+        rearrange_tensors(d1.ptr, d2.ptr, shape, esz, 3, "write")
+    with pytest.raises(KvError):
+        rearrange_tensors(d1.ptr, d2.ptr, shape, esz, d, "sideways")

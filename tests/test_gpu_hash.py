@@ -162,3 +162,18 @@ def test_device_resident_api_and_large_batch_properties(gpu, oracle):
     # bad workspace is rejected, not overrun
     assert L.kvdp_hash_token_blocks(d_tok.ptr, d_off.ptr, n_req, total, 64, 1, d_boff.ptr, d_bh.ptr, d_sh.ptr,
                                     d_ws.ptr, 8, 0, None) == gpu.KVDP_EINVAL
+
+
+def test_stored_event_from_parts_like_the_c_bindings(gpu, oracle):
+    """lib/bindings/c/src/lib.rs:175-227: blocks are published until the first one that is not full; tokens_hash is the
+    seed-1337 un-chained hash of each block; block_hash is the engine's id."""
+    from dynamo_exp_b200.tokens import kv_event_create_stored_from_parts
+    bs = 16
+    toks = tokens_for(3, 5 * bs)
+    ev = kv_event_create_stored_from_parts(7, toks, [bs, bs, bs, 5, bs], [100, 101, 102, 103, 104], bs, parent_hash=99)
+    blocks = ev["data"]["stored"]["blocks"]
+    assert ev["event_id"] == 7 and ev["data"]["stored"]["parent_hash"] == 99
+    assert [b["block_hash"] for b in blocks] == [100, 101, 102]          # stops at the short block
+    want = oracle.indexer_block_hashes(toks[:3 * bs], bs)
+    assert [b["tokens_hash"] for b in blocks] == [int(x) for x in want]
+    assert kv_event_create_stored_from_parts(8, toks, [3], [1], bs)["data"]["stored"]["blocks"] == []
