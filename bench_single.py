@@ -269,7 +269,7 @@ def hash_bench(torch, lib, steps, warmup, peak):
     from tests.util import mix64
     L = lib.lib()
     isls = [512, 1024, 2048, 4096, 8192, 16384, 32768]
-    n_req = 7 * 2048
+    n_req = 7 * 8192          # 57 344 requests, 8.3 M blocks, 2.1 GB of tokens per batch (>> L2)
     lens = np.array([isls[i % 7] for i in range(n_req)], dtype=np.int64)
     offs = np.zeros(n_req + 1, dtype=np.int64)
     offs[1:] = np.cumsum(lens)
@@ -337,13 +337,21 @@ def hash_bench(torch, lib, steps, warmup, peak):
     b.record(streams[0])
     torch.cuda.synchronize()
     sec_un = a.elapsed_time(b) / 1e3 / steps
-    out = {"hashes_per_s": nblk / sec, "tokens_per_s": total / sec, "ms_per_batch": sec * 1e3, "requests": n_req,
-           "blocks": nblk, "launches_per_batch": 3, "streams": 2,
+    out = {"hashes_per_s": nblk / sec_serial, "tokens_per_s": total / sec_serial, "ms_per_batch": sec_serial * 1e3,
+           "requests": n_req, "blocks": nblk, "launches_per_batch": 5,
+           "semantics": "lib/tokens: block_hash + chained sequence_hash per full 64-token block, one stream",
+           "two_stream_pipeline": {"hashes_per_s": nblk / sec, "ms_per_batch": sec * 1e3},
            "unchained_router_form": {"hashes_per_s": nblk / sec_un, "ms_per_batch": sec_un * 1e3,
-                                     "hbm_frac": nblk * 264 / sec_un / GB / peak},
-           "single_stream": {"hashes_per_s": nblk / sec_serial, "ms_per_batch": sec_serial * 1e3},
-           "roofline": {"bound": "hbm", "achieved": nblk * 272 / sec / GB, "peak": peak, "unit": "GB/s",
-                        "frac": nblk * 272 / sec / GB / peak, "traffic": ncu_traffic("kvdp_hash_blocks_tma")}}
+                                     "semantics": "kv_router LocalBlockHash (seed 1337), scan + block-hash kernels"},
+           # dominant kernel = the block-hash kernel; measured through the un-chained call (scan kernels included,
+           # so this is a lower bound for the kernel itself); 264 B/block = 256 read + 8 written
+           "roofline": {"bound": "hbm", "achieved": nblk * 264 / sec_un / GB, "peak": peak, "unit": "GB/s",
+                        "frac": nblk * 264 / sec_un / GB / peak, "kernel": "kvdp_hash_blocks_tma<4,8>",
+                        "algorithmic_bytes_per_launch": nblk * 264,
+                        "traffic": ncu_traffic("kvdp_hash_blocks_tma"),
+                        "traffic_note": "ncu traffic was captured on the 2.08 M-block batch (0.5506 GB vs 0.5493 GB "
+                                        "algorithmic, ratio 1.002)"},
+           "chained_hbm_frac": nblk * 272 / sec_serial / GB / peak}
     # e2e: pinned host tokens -> device -> hashes back on the host, through kvdp_hash_token_blocks_host
     n_e = 7 * 256
     lens_e = lens[:n_e]

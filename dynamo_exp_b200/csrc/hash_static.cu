@@ -7,15 +7,15 @@
 // Such a caller can still pass its input and output buffers, but it has nowhere to get the scan scratch that
 // kvdp_hash_token_blocks() asks for. This entry point carries that scratch inside the library image instead.
 //
-// The scratch is a file-scope __device__ array, so every GPU that loads libkvdp.so holds kStaticScratchBytes (16 KiB)
+// The scratch is a file-scope __device__ array, so every GPU that loads libkvdp.so holds kStaticScratchBytes (64 KiB)
 // of it from load until exit, whether or not this entry point is ever called.
 #include <mutex>
 
 #include "common.cuh"
 
-constexpr size_t kStaticScratchBytes = 16 * 1024;
+constexpr size_t kStaticScratchBytes = 64 * 1024;
 
-// Scan partials for the block-count prefix sum (one int64 per 4096 requests). In HOST code this name is only a
+// Scan partials for the block-count prefix sum (one int64 per 1024 requests). In HOST code this name is only a
 // stand-in symbol, not an address a kernel can use; the device address is looked up per device below.
 static __device__ __align__(256) unsigned char g_hash_scan_scratch[kStaticScratchBytes];
 

@@ -236,7 +236,7 @@ int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, i
                            kvdp_stream_t stream);
 /* The same hashing for a caller that must not allocate device memory: a thread inside an engine whose memory manager
  * took the whole GPU for the KV cache at start-up, or code where a cudaMalloc (which serialises the device) is not
- * acceptable. It takes no workspace; the scan scratch lives in a 16 KiB __device__ array inside the library (held by
+ * acceptable. It takes no workspace; the scan scratch lives in a 64 KiB __device__ array inside the library (held by
  * every GPU that loads libkvdp.so, until exit). Limits and rules:
  *   - at most KVDP_HASH_NOALLOC_MAX_REQUESTS requests per call; more returns KVDP_ERANGE and launches nothing;
  *   - it calls no cudaMalloc / cudaFree / allocating routine; inputs and outputs are still the caller's buffers;

@@ -3,7 +3,8 @@
 
 It must produce exactly what kvdp_hash_token_blocks produces with a caller-supplied workspace, call after call, even
 though its scratch is one array shared by every call and still holds the previous call's partial sums. The batches
-here are larger than 65 535 requests on purpose: only then does the block-count scan go through the scratch at all.
+here hold tens of thousands of requests on purpose: only above 2 048 requests does the block-count scan go through the
+scratch at all.
 This file sorts last so that a run stopping at the first failure has already been through every other test.
 """
 import ctypes as C
@@ -52,7 +53,7 @@ def run_both(gpu, toks, offs, block_size, salt, flags=0):
 
 
 def test_noalloc_matches_workspace_entry_twice_in_a_row(gpu):
-    # call 1: 70 001 requests -> 18 scan partials land in the built-in scratch
+    # call 1: 70 001 requests -> 69 scan partials land in the built-in scratch
     toks, offs = make_batch(70001, seed=1, max_len=200)
     (b0, h0, s0), (b1, h1, s1) = run_both(gpu, toks, offs, 64, 1337)
     assert b0[-1] > 0
