@@ -99,6 +99,7 @@ PROTOTYPES = {
     "kvdp_xfer_signal": (_i, [_vp, _vp, _u32]),
     "kvdp_xfer_sync": (_i, [_vp]),
     "kvdp_plan_launch": (_i, [_vp, _vp, _vp, _i32, _i32, _i32, _vp]),
+    "kvdp_stream_synchronize": (_i, [_vp]),
     "kvdp_stream_wait_flag": (_i, [_vp, _vp, _u32]),
     "kvdp_peer_enable": (_i, [_i32, _i32]),
     "kvdp_ipc_export": (_i, [_vp, _vp]),
@@ -115,6 +116,15 @@ PROTOTYPES = {
     "kvdp_hash_token_blocks_noalloc": (_i, [_vp, _vp, _i64, _i64, _i32, _u64, _vp, _vp, _vp, _u32, _vp]),
     "kvdp_hash_token_blocks_host": (_i, [_vp, _vp, _i64, _i32, _u64, _vp, _vp, _vp, _u32, _i32]),
     "kvdp_xxh3_64_batch": (_i, [_vp, _i64, _i64, _u64, _vp, _vp]),
+    "kvdp_index_create": (_i, [_pp, _i64, _i32, _i32]),
+    "kvdp_index_destroy": (_i, [_vp]),
+    "kvdp_index_stream": (_vp, [_vp]),
+    "kvdp_index_apply_stored": (_i, [_vp, _i32, _i32, _u64, _vp, _vp, _i32]),
+    "kvdp_index_apply_removed": (_i, [_vp, _i32, _vp, _i32]),
+    "kvdp_index_remove_worker": (_i, [_vp, _i32]),
+    "kvdp_index_flush": (_i, [_vp]),
+    "kvdp_index_find_matches": (_i, [_vp, _vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp]),
+    "kvdp_index_stat": (_i64, [_vp, _i32, _u64]),
 }
 
 _lib = None

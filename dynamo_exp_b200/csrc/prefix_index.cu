@@ -1,0 +1,443 @@
+// prefix_index.cu — the KV router's prefix index with batched GPU lookups (SURVEY §8f "next-1").
+//
+// Reference: RadixTree in lib/llm/src/kv_router/indexer.rs:187-387 — a tree of blocks keyed by LocalBlockHash whose
+// nodes carry the set of workers holding that block; `find_matches` (:239-277) walks a request's block hashes from the
+// root and counts, per worker, how many leading blocks it holds; `apply_event` (:284-378) inserts / removes blocks per
+// worker through a per-worker table keyed by the engine's ExternalSequenceBlockHash; `remove_worker` (:380-386).
+// There it is a single-threaded actor over Rc<RefCell<..>> nodes, one request at a time.
+//
+// Here the structure is split by what each side is good at:
+//   * event application stays on the host, serial and in event order (it IS order-dependent), in a plain C++ mirror of
+//     the reference's semantics — including blocks shared between parents through the per-worker table and the
+//     "last worker left: drop all children" rule;
+//   * every change is mirrored into two flat device arrays: node records {worker bitset, generation} and an
+//     open-addressing edge table keyed by (parent node, parent generation, tokens hash) -> child node. Dropping a
+//     node's children is a generation bump (stale edges simply stop matching);
+//   * find_matches runs for a whole batch of requests in one launch, one thread per request, each step one 32-byte
+//     edge probe + one 16-byte node read; per-worker scores are kept as bit-sliced counters (one 64-bit plane per
+//     binary digit), so adding a node's worker set costs a ripple of AND/XORs instead of a 64-way loop.
+// Up to 64 workers per index (one bitset word); the host layer maps WorkerId -> slot.
+#include <string.h>
+
+#include <algorithm>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+
+namespace kvdp {
+namespace {
+
+struct NodeRec {   // 16 bytes
+  uint64_t workers;
+  uint32_t gen;
+  uint32_t pad;
+};
+struct EdgeRec {   // 32 bytes: one sector per probe
+  uint64_t hash;
+  uint32_t parent;
+  uint32_t gen;
+  uint32_t child;
+  uint32_t used;
+  uint64_t pad;
+};
+
+__host__ __device__ __forceinline__ uint64_t edge_slot_hash(uint64_t hash, uint32_t parent, uint32_t gen) {
+  uint64_t x = hash ^ (((uint64_t)parent << 32) | gen) * 0x9E3779B97F4A7C15ULL;
+  x ^= x >> 32;
+  x *= 0xD6E8FEB86659FD93ULL;
+  x ^= x >> 32;
+  return x;
+}
+
+constexpr int kPlanes = 16;  // bit-sliced counters: depths up to 65535 blocks
+
+__global__ void __launch_bounds__(128) kvdp_index_find_kernel(const NodeRec* __restrict__ nodes,
+                                                              const EdgeRec* __restrict__ edges, uint64_t mask,
+                                                              const uint64_t* __restrict__ hashes,
+                                                              const int64_t* __restrict__ seq_offsets, int64_t n_req,
+                                                              int early_exit, int num_workers,
+                                                              uint32_t* __restrict__ scores,
+                                                              int32_t* __restrict__ matched_depth) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_req) return;
+  const int64_t s0 = seq_offsets[r], s1 = seq_offsets[r + 1];
+  uint64_t plane[kPlanes];
+#pragma unroll
+  for (int p = 0; p < kPlanes; ++p) plane[p] = 0;
+  uint32_t node = 0, gen = nodes[0].gen;
+  int depth = 0;
+  for (int64_t i = s0; i < s1; ++i) {
+    const uint64_t h = __ldg(hashes + i);
+    uint64_t slot = edge_slot_hash(h, node, gen) & mask;
+    uint32_t child = 0xffffffffu;
+    for (;;) {
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(edges + slot));       // hash, parent, gen
+      const uint2 b = __ldg(reinterpret_cast<const uint2*>(edges + slot) + 2);   // child, used
+      if (b.y == 0) break;                                                        // empty slot: not present
+      const uint64_t eh = (uint64_t)a.x | ((uint64_t)a.y << 32);
+      if (eh == h && a.z == node && a.w == gen) {
+        child = b.x;
+        break;
+      }
+      slot = (slot + 1) & mask;
+    }
+    if (child == 0xffffffffu) break;
+    const uint4 nr = __ldg(reinterpret_cast<const uint4*>(nodes + child));
+    uint64_t carry = (uint64_t)nr.x | ((uint64_t)nr.y << 32);
+    const int nworkers = __popcll(carry);
+    ++depth;
+#pragma unroll
+    for (int p = 0; p < kPlanes; ++p) {   // planes += worker mask
+      const uint64_t t = plane[p] & carry;
+      plane[p] ^= carry;
+      carry = t;
+    }
+    if (early_exit && nworkers == 1) break;
+    node = child;
+    gen = nr.z;
+  }
+  if (matched_depth) matched_depth[r] = depth;
+  for (int w = 0; w < num_workers; ++w) {
+    uint32_t c = 0;
+#pragma unroll
+    for (int p = 0; p < kPlanes; ++p) c |= (uint32_t)((plane[p] >> w) & 1ULL) << p;
+    scores[r * (int64_t)num_workers + w] = c;
+  }
+}
+
+template <typename Rec>
+__global__ void kvdp_index_scatter_kernel(Rec* __restrict__ table, const uint32_t* __restrict__ idx,
+                                          const Rec* __restrict__ recs, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) table[idx[i]] = recs[i];
+}
+
+struct HostNode {
+  std::unordered_map<uint64_t, uint32_t> children;  // tokens hash -> node id
+  uint64_t workers = 0;
+  uint32_t gen = 0;
+};
+
+}  // namespace
+}  // namespace kvdp
+
+using namespace kvdp;
+
+struct kvdp_index {
+  int device = -1;
+  int max_workers = 64;
+  int64_t max_nodes = 0;
+  uint64_t capacity = 0;  // edge table slots (power of two)
+  uint64_t live_slots = 0;
+  std::vector<HostNode> nodes;
+  std::unordered_map<uint64_t, uint32_t> lookup[64];
+  bool lookup_present[64] = {};
+  std::vector<EdgeRec> h_edges;
+  NodeRec* d_nodes = nullptr;
+  EdgeRec* d_edges = nullptr;
+  std::vector<uint32_t> dirty_nodes, dirty_edges;
+  std::vector<uint8_t> node_dirty_flag, edge_dirty_flag;
+  // upload staging (grown on demand)
+  uint32_t* d_idx = nullptr;
+  void* d_recs = nullptr;
+  size_t stage_cap = 0;
+  cudaStream_t stream = nullptr;
+  bool full_upload_needed = true;
+};
+
+namespace {
+
+void mark_node(kvdp_index* ix, uint32_t n) {
+  if (!ix->node_dirty_flag[n]) {
+    ix->node_dirty_flag[n] = 1;
+    ix->dirty_nodes.push_back(n);
+  }
+}
+
+int insert_edge(kvdp_index* ix, uint32_t parent, uint64_t hash, uint32_t child) {
+  const uint32_t gen = ix->nodes[parent].gen;
+  const uint64_t mask = ix->capacity - 1;
+  uint64_t slot = edge_slot_hash(hash, parent, gen) & mask;
+  for (uint64_t probes = 0; probes < ix->capacity; ++probes) {
+    EdgeRec& e = ix->h_edges[slot];
+    if (!e.used) {
+      e.hash = hash;
+      e.parent = parent;
+      e.gen = gen;
+      e.child = child;
+      e.used = 1;
+      ++ix->live_slots;
+      if (!ix->edge_dirty_flag[slot]) {
+        ix->edge_dirty_flag[slot] = 1;
+        ix->dirty_edges.push_back((uint32_t)slot);
+      }
+      return 0;
+    }
+    slot = (slot + 1) & mask;
+  }
+  return fail(KVDP_ERANGE, "prefix index: edge table full");
+}
+
+// Rebuild the edge table from the authoritative host maps (drops the dead generations).
+int rebuild_edges(kvdp_index* ix) {
+  std::fill(ix->h_edges.begin(), ix->h_edges.end(), EdgeRec{});
+  std::fill(ix->edge_dirty_flag.begin(), ix->edge_dirty_flag.end(), 0);
+  ix->dirty_edges.clear();
+  ix->live_slots = 0;
+  for (uint32_t p = 0; p < ix->nodes.size(); ++p)
+    for (auto& kv : ix->nodes[p].children)
+      if (int rc = insert_edge(ix, p, kv.first, kv.second)) return rc;
+  ix->full_upload_needed = true;
+  return 0;
+}
+
+int new_node(kvdp_index* ix, uint32_t* out) {
+  if ((int64_t)ix->nodes.size() >= ix->max_nodes)
+    return fail(KVDP_ERANGE, "prefix index: node capacity %lld exhausted", (long long)ix->max_nodes);
+  ix->nodes.emplace_back();
+  *out = (uint32_t)ix->nodes.size() - 1;
+  mark_node(ix, *out);
+  return 0;
+}
+
+int ensure_stage(kvdp_index* ix, size_t n) {
+  if (n <= ix->stage_cap) return 0;
+  if (ix->d_idx) cudaFree(ix->d_idx);
+  if (ix->d_recs) cudaFree(ix->d_recs);
+  ix->d_idx = nullptr;
+  ix->d_recs = nullptr;
+  ix->stage_cap = 0;
+  const size_t cap = std::max<size_t>(n * 2, 4096);
+  KVDP_CUDA(cudaMalloc(&ix->d_idx, cap * sizeof(uint32_t)));
+  KVDP_CUDA(cudaMalloc(&ix->d_recs, cap * sizeof(EdgeRec)));
+  ix->stage_cap = cap;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int kvdp_index_create(kvdp_index** out, int64_t max_nodes, int32_t max_workers, int32_t device) {
+  if (!out) return fail(KVDP_EINVAL, "kvdp_index_create: NULL out");
+  *out = nullptr;
+  if (max_nodes < 2 || max_nodes > ((int64_t)1 << 31)) return fail(KVDP_EINVAL, "prefix index: max_nodes out of range");
+  if (max_workers < 1 || max_workers > 64) return fail(KVDP_EINVAL, "prefix index: max_workers must be 1..64");
+  kvdp_index* ix = new kvdp_index();
+  ix->device = device;
+  if (ix->device < 0) cudaGetDevice(&ix->device);
+  ix->max_workers = max_workers;
+  ix->max_nodes = max_nodes;
+  uint64_t cap = 1024;
+  while (cap < (uint64_t)max_nodes * 4) cap <<= 1;  // load factor <= 0.25 for live edges, room for dead generations
+  ix->capacity = cap;
+  ix->h_edges.assign(cap, EdgeRec{});
+  ix->edge_dirty_flag.assign(cap, 0);
+  ix->node_dirty_flag.assign((size_t)max_nodes, 0);
+  ix->nodes.reserve((size_t)std::min<int64_t>(max_nodes, 1 << 20));
+  ix->nodes.emplace_back();  // root
+  DeviceGuard g(ix->device);
+  cudaError_t e = cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMalloc(&ix->d_nodes, sizeof(NodeRec) * (size_t)max_nodes);
+  if (e == cudaSuccess) e = cudaMalloc(&ix->d_edges, sizeof(EdgeRec) * cap);
+  if (e == cudaSuccess) e = cudaMemset(ix->d_nodes, 0, sizeof(NodeRec) * (size_t)max_nodes);
+  if (e == cudaSuccess) e = cudaMemset(ix->d_edges, 0, sizeof(EdgeRec) * cap);
+  if (e != cudaSuccess) {
+    kvdp_index_destroy(ix);
+    return fail((int)e, "prefix index: device allocation failed: %s", cudaGetErrorString(e));
+  }
+  ix->full_upload_needed = false;  // both sides are all-zero
+  *out = ix;
+  return 0;
+}
+
+int kvdp_index_destroy(kvdp_index* ix) {
+  if (!ix) return 0;
+  DeviceGuard g(ix->device);
+  if (ix->stream) {
+    cudaStreamSynchronize(ix->stream);
+    cudaStreamDestroy(ix->stream);
+  }
+  if (ix->d_nodes) cudaFree(ix->d_nodes);
+  if (ix->d_edges) cudaFree(ix->d_edges);
+  if (ix->d_idx) cudaFree(ix->d_idx);
+  if (ix->d_recs) cudaFree(ix->d_recs);
+  delete ix;
+  return 0;
+}
+
+kvdp_stream_t kvdp_index_stream(kvdp_index* ix) { return ix ? (kvdp_stream_t)ix->stream : nullptr; }
+
+// indexer.rs:296-343. Returns 1 (and changes nothing) when the parent block is unknown for this worker.
+int kvdp_index_apply_stored(kvdp_index* ix, int32_t worker, int32_t has_parent, uint64_t parent_hash,
+                            const uint64_t* block_hashes, const uint64_t* tokens_hashes, int32_t n) {
+  if (!ix) return fail(KVDP_EINVAL, "kvdp_index_apply_stored: NULL handle");
+  if (worker < 0 || worker >= ix->max_workers) return fail(KVDP_EINVAL, "prefix index: worker slot %d out of range", worker);
+  if (n < 0 || (n > 0 && (!block_hashes || !tokens_hashes))) return fail(KVDP_EINVAL, "prefix index: bad block arrays");
+  ix->lookup_present[worker] = true;
+  auto& lk = ix->lookup[worker];
+  uint32_t current = 0;
+  if (has_parent) {
+    auto it = lk.find(parent_hash);
+    if (it == lk.end()) return 1;  // "Failed to find parent block; skipping store operation"
+    current = it->second;
+  }
+  if (ix->live_slots + (uint64_t)n > ix->capacity / 2)
+    if (int rc = rebuild_edges(ix)) return rc;
+  for (int32_t i = 0; i < n; ++i) {
+    uint32_t block;
+    auto& children = ix->nodes[current].children;
+    auto c = children.find(tokens_hashes[i]);
+    if (c != children.end()) {
+      block = c->second;
+    } else {
+      auto known = lk.find(block_hashes[i]);
+      if (known != lk.end()) {
+        block = known->second;  // the worker already has this block under another parent: share it
+      } else if (int rc = new_node(ix, &block)) {
+        return rc;
+      }
+      ix->nodes[current].children.emplace(tokens_hashes[i], block);
+      if (int rc = insert_edge(ix, current, tokens_hashes[i], block)) return rc;
+    }
+    HostNode& b = ix->nodes[block];
+    if (!(b.workers >> worker & 1ULL)) {
+      b.workers |= 1ULL << worker;
+      mark_node(ix, block);
+    }
+    lk[block_hashes[i]] = block;
+    current = block;
+  }
+  return 0;
+}
+
+// indexer.rs:344-376
+int kvdp_index_apply_removed(kvdp_index* ix, int32_t worker, const uint64_t* block_hashes, int32_t n) {
+  if (!ix) return fail(KVDP_EINVAL, "kvdp_index_apply_removed: NULL handle");
+  if (worker < 0 || worker >= ix->max_workers) return fail(KVDP_EINVAL, "prefix index: worker slot %d out of range", worker);
+  if (n < 0 || (n > 0 && !block_hashes)) return fail(KVDP_EINVAL, "prefix index: bad block array");
+  ix->lookup_present[worker] = true;
+  auto& lk = ix->lookup[worker];
+  for (int32_t i = 0; i < n; ++i) {
+    auto it = lk.find(block_hashes[i]);
+    if (it == lk.end()) continue;  // "Failed to find block to remove; skipping remove operation"
+    HostNode& b = ix->nodes[it->second];
+    b.workers &= ~(1ULL << worker);
+    if (b.workers == 0) {
+      b.children.clear();  // no worker holds this block, so none holds its descendants through it
+      ++b.gen;             // device side: every edge out of this node stops matching
+    }
+    mark_node(ix, it->second);
+    lk.erase(it);
+  }
+  return 0;
+}
+
+// indexer.rs:380-386
+int kvdp_index_remove_worker(kvdp_index* ix, int32_t worker) {
+  if (!ix) return fail(KVDP_EINVAL, "kvdp_index_remove_worker: NULL handle");
+  if (worker < 0 || worker >= ix->max_workers) return fail(KVDP_EINVAL, "prefix index: worker slot %d out of range", worker);
+  if (!ix->lookup_present[worker]) return 0;
+  for (auto& kv : ix->lookup[worker]) {
+    HostNode& b = ix->nodes[kv.second];
+    if (b.workers >> worker & 1ULL) {
+      b.workers &= ~(1ULL << worker);
+      mark_node(ix, kv.second);
+    }
+  }
+  ix->lookup[worker].clear();
+  ix->lookup_present[worker] = false;
+  return 0;
+}
+
+// Push every pending change to the device (asynchronous on the index's stream).
+int kvdp_index_flush(kvdp_index* ix) {
+  if (!ix) return fail(KVDP_EINVAL, "kvdp_index_flush: NULL handle");
+  DeviceGuard g(ix->device);
+  if (ix->full_upload_needed) {
+    KVDP_CUDA(cudaMemcpyAsync(ix->d_edges, ix->h_edges.data(), sizeof(EdgeRec) * ix->capacity, cudaMemcpyHostToDevice,
+                              ix->stream));
+    KVDP_CUDA(cudaStreamSynchronize(ix->stream));  // pageable source: keep the host table stable until copied
+    for (uint32_t s : ix->dirty_edges) ix->edge_dirty_flag[s] = 0;
+    ix->dirty_edges.clear();
+    ix->full_upload_needed = false;
+  }
+  const size_t ne = ix->dirty_edges.size(), nn = ix->dirty_nodes.size();
+  if (ne == 0 && nn == 0) return 0;
+  if (int rc = ensure_stage(ix, std::max(ne, nn))) return rc;
+  if (ne) {
+    std::vector<EdgeRec> recs(ne);
+    for (size_t i = 0; i < ne; ++i) recs[i] = ix->h_edges[ix->dirty_edges[i]];
+    KVDP_CUDA(cudaMemcpyAsync(ix->d_idx, ix->dirty_edges.data(), ne * sizeof(uint32_t), cudaMemcpyHostToDevice, ix->stream));
+    KVDP_CUDA(cudaMemcpyAsync(ix->d_recs, recs.data(), ne * sizeof(EdgeRec), cudaMemcpyHostToDevice, ix->stream));
+    kvdp_index_scatter_kernel<EdgeRec><<<(unsigned)((ne + 255) / 256), 256, 0, ix->stream>>>(
+        ix->d_edges, ix->d_idx, (const EdgeRec*)ix->d_recs, (int)ne);
+    KVDP_CUDA(cudaStreamSynchronize(ix->stream));
+    for (uint32_t s : ix->dirty_edges) ix->edge_dirty_flag[s] = 0;
+    ix->dirty_edges.clear();
+  }
+  if (nn) {
+    std::vector<NodeRec> recs(nn);
+    for (size_t i = 0; i < nn; ++i) {
+      const HostNode& h = ix->nodes[ix->dirty_nodes[i]];
+      recs[i] = NodeRec{h.workers, h.gen, 0};
+    }
+    KVDP_CUDA(cudaMemcpyAsync(ix->d_idx, ix->dirty_nodes.data(), nn * sizeof(uint32_t), cudaMemcpyHostToDevice, ix->stream));
+    KVDP_CUDA(cudaMemcpyAsync(ix->d_recs, recs.data(), nn * sizeof(NodeRec), cudaMemcpyHostToDevice, ix->stream));
+    kvdp_index_scatter_kernel<NodeRec><<<(unsigned)((nn + 255) / 256), 256, 0, ix->stream>>>(
+        ix->d_nodes, ix->d_idx, (const NodeRec*)ix->d_recs, (int)nn);
+    KVDP_CUDA(cudaStreamSynchronize(ix->stream));
+    for (uint32_t n : ix->dirty_nodes) ix->node_dirty_flag[n] = 0;
+    ix->dirty_nodes.clear();
+  }
+  KVDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Batched RadixTree::find_matches (indexer.rs:239-277) for n_req requests given as CSR sequences of LocalBlockHash on
+// the device. scores is [n_req][num_workers] (u32, worker slot order); matched_depth[n_req] may be NULL. Pending
+// changes are flushed first. Asynchronous on `stream` (NULL = the index's own stream).
+int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int64_t* d_seq_offsets, int64_t n_req,
+                            int32_t early_exit, int32_t num_workers, uint32_t* d_scores, int32_t* d_matched_depth,
+                            kvdp_stream_t stream_) {
+  if (!ix) return fail(KVDP_EINVAL, "kvdp_index_find_matches: NULL handle");
+  if (n_req < 0) return fail(KVDP_EINVAL, "prefix index: negative n_req");
+  if (num_workers < 1 || num_workers > ix->max_workers) return fail(KVDP_EINVAL, "prefix index: num_workers out of range");
+  if (n_req == 0) return 0;
+  if (!d_seq_offsets || !d_scores) return fail(KVDP_EINVAL, "prefix index: NULL pointer");
+  if (int rc = kvdp_index_flush(ix)) return rc;
+  DeviceGuard g(ix->device);
+  cudaStream_t stream = stream_ ? (cudaStream_t)stream_ : ix->stream;
+  kvdp_index_find_kernel<<<(unsigned)((n_req + 127) / 128), 128, 0, stream>>>(
+      ix->d_nodes, ix->d_edges, ix->capacity - 1, d_hashes, d_seq_offsets, n_req, early_exit, num_workers, d_scores,
+      d_matched_depth);
+  KVDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// sizes of the host-side structures, for the reference tests' assertions:
+// what = 0: number of nodes; 1: live edges out of `arg` (node id); 2: entries in worker `arg`'s lookup table;
+//        3: popcount of node `arg`'s worker set; 4: child of the root for tokens hash `arg` (node id or -1);
+//        5: workers that ever had a lookup table and still do
+int64_t kvdp_index_stat(kvdp_index* ix, int32_t what, uint64_t arg) {
+  if (!ix) return -1;
+  switch (what) {
+    case 0: return (int64_t)ix->nodes.size();
+    case 1: return arg < ix->nodes.size() ? (int64_t)ix->nodes[arg].children.size() : -1;
+    case 2: return arg < 64 ? (int64_t)ix->lookup[arg].size() : -1;
+    case 3: return arg < ix->nodes.size() ? (int64_t)__builtin_popcountll(ix->nodes[arg].workers) : -1;
+    case 4: {
+      auto it = ix->nodes[0].children.find(arg);
+      return it == ix->nodes[0].children.end() ? -1 : (int64_t)it->second;
+    }
+    case 5: {
+      int64_t c = 0;
+      for (int w = 0; w < 64; ++w) c += ix->lookup_present[w] ? 1 : 0;
+      return c;
+    }
+    default: return -1;
+  }
+}
+
+}  // extern "C"

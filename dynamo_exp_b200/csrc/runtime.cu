@@ -215,6 +215,11 @@ int kvdp_ipc_close(void* mapped_ptr) {
   return 0;
 }
 
+int kvdp_stream_synchronize(kvdp_stream_t stream) {
+  KVDP_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return 0;
+}
+
 int kvdp_stream_wait_flag(kvdp_stream_t stream, uint32_t* flag, uint32_t value) {
   if (!flag) return fail(KVDP_EINVAL, "kvdp_stream_wait_flag: NULL flag");
   // resolved at run time so that libkvdp.so has no link-time dependency on libcuda.so.1 (it must load on a

@@ -1,0 +1,260 @@
+"""Host-side mirror of the KV router's indexer (lib/llm/src/kv_router/indexer.rs, protocols.rs) over libkvdp.so.
+
+`RadixTree` / `KvIndexer` keep the reference's method names (apply_event, find_matches, find_matches_for_request,
+remove_worker); the data types (`RouterEvent`, `KvCacheEvent`, `KvCacheStoreData`, ...) serialise to the same JSON the
+reference's serde derives produce (protocols.rs:70-121: `{"stored": {...}}` / `{"removed": {...}}`, hashes as plain
+u64 numbers). New here: `find_matches_batch`, which scores a whole batch of requests in one GPU launch, and
+`find_matches_for_requests`, which also hashes the token blocks on the GPU first (kvdp_hash_token_blocks, seed 1337).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Union
+
+import numpy as np
+
+from . import _lib
+from .storage import KvError
+from .tokens import XXH3_SEED, _as_u32
+
+WorkerId = int
+MAX_WORKERS = 64
+
+
+# ---------------------------------------------------------------------------------------------- protocol types
+@dataclass
+class KvCacheStoredBlockData:            # protocols.rs:107-113
+    block_hash: int                      # ExternalSequenceBlockHash
+    tokens_hash: int                     # LocalBlockHash
+
+
+@dataclass
+class KvCacheStoreData:                  # protocols.rs:98-104
+    parent_hash: Optional[int]
+    blocks: List[KvCacheStoredBlockData]
+
+
+@dataclass
+class KvCacheRemoveData:                 # protocols.rs:116-120
+    block_hashes: List[int]
+
+
+@dataclass
+class KvCacheEvent:                      # protocols.rs:79-85; data is `Stored(..)` or `Removed(..)`
+    event_id: int
+    data: Union[KvCacheStoreData, KvCacheRemoveData]
+
+    def to_dict(self) -> dict:
+        if isinstance(self.data, KvCacheStoreData):
+            d = {"stored": {"parent_hash": self.data.parent_hash,
+                            "blocks": [{"block_hash": b.block_hash, "tokens_hash": b.tokens_hash}
+                                       for b in self.data.blocks]}}
+        else:
+            d = {"removed": {"block_hashes": list(self.data.block_hashes)}}
+        return {"event_id": self.event_id, "data": d}
+
+    @staticmethod
+    def from_dict(d: dict) -> "KvCacheEvent":
+        data = d["data"]
+        if "stored" in data:
+            s = data["stored"]
+            return KvCacheEvent(d["event_id"], KvCacheStoreData(
+                s.get("parent_hash"), [KvCacheStoredBlockData(b["block_hash"], b["tokens_hash"]) for b in s["blocks"]]))
+        if "removed" in data:
+            return KvCacheEvent(d["event_id"], KvCacheRemoveData(list(data["removed"]["block_hashes"])))
+        raise KvError("KvCacheEventData must be `stored` or `removed`")
+
+
+@dataclass
+class RouterEvent:                       # indexer.rs:137-160
+    worker_id: WorkerId
+    event: KvCacheEvent
+
+    def to_json(self) -> str:
+        return json.dumps({"worker_id": self.worker_id, "event": self.event.to_dict()}, separators=(",", ":"))
+
+    @staticmethod
+    def from_json(s: str) -> "RouterEvent":
+        d = json.loads(s)
+        return RouterEvent(d["worker_id"], KvCacheEvent.from_dict(d["event"]))
+
+
+@dataclass
+class KvCacheEvents:                     # protocols.rs:70-76
+    events: List[KvCacheEvent]
+    shutdown: bool = False
+
+    def to_json(self) -> str:
+        return json.dumps({"events": [e.to_dict() for e in self.events], "shutdown": self.shutdown},
+                          separators=(",", ":"))
+
+    @staticmethod
+    def from_json(s: str) -> "KvCacheEvents":
+        d = json.loads(s)
+        return KvCacheEvents([KvCacheEvent.from_dict(e) for e in d["events"]], bool(d["shutdown"]))
+
+
+@dataclass
+class OverlapScores:                     # indexer.rs:390-436
+    scores: Dict[WorkerId, int] = field(default_factory=dict)
+    frequencies: List[int] = field(default_factory=list)
+
+
+# ---------------------------------------------------------------------------------------------- the index
+class RadixTree:
+    """reference: indexer.rs:187-387. Events are applied on the host inside libkvdp.so; lookups run on the GPU."""
+
+    def __init__(self, max_nodes: int = 1 << 20, device: int = -1):
+        _lib.require_gpu()
+        h = C.c_void_p()
+        _lib.check(_lib.lib().kvdp_index_create(C.byref(h), int(max_nodes), MAX_WORKERS, int(device)))
+        self._h = h
+        self._slot: Dict[WorkerId, int] = {}
+        self._worker_of_slot: List[Optional[WorkerId]] = [None] * MAX_WORKERS
+
+    def _slot_of(self, worker_id: WorkerId, create: bool) -> Optional[int]:
+        s = self._slot.get(worker_id)
+        if s is None and create:
+            free = [i for i, w in enumerate(self._worker_of_slot) if w is None]
+            if not free:
+                raise KvError(f"the prefix index holds at most {MAX_WORKERS} distinct worker ids over its lifetime")
+            s = free[0]
+            self._slot[worker_id] = s
+            self._worker_of_slot[s] = worker_id
+        return s
+
+    def apply_event(self, event: RouterEvent) -> None:
+        L = _lib.lib()
+        slot = self._slot_of(event.worker_id, True)
+        data = event.event.data
+        if isinstance(data, KvCacheStoreData):
+            bh = np.array([b.block_hash for b in data.blocks], dtype=np.uint64)
+            th = np.array([b.tokens_hash for b in data.blocks], dtype=np.uint64)
+            rc = L.kvdp_index_apply_stored(self._h, slot, 0 if data.parent_hash is None else 1,
+                                           int(data.parent_hash or 0), bh.ctypes.data if bh.size else None,
+                                           th.ctypes.data if th.size else None, bh.size)
+            if rc < 0:
+                _lib.check(rc)
+            # rc == 1: parent unknown, the reference logs a warning and skips the event (indexer.rs:305-315)
+        else:
+            bh = np.array(list(data.block_hashes), dtype=np.uint64)
+            _lib.check(L.kvdp_index_apply_removed(self._h, slot, bh.ctypes.data if bh.size else None, bh.size))
+
+    def remove_worker(self, worker: WorkerId) -> None:
+        slot = self._slot_of(worker, False)
+        if slot is None:
+            return
+        _lib.check(_lib.lib().kvdp_index_remove_worker(self._h, slot))
+        # The slot stays bound to this worker id: like the reference, a block whose lookup entry was overwritten keeps
+        # the removed worker in its set (remove_worker only visits the lookup table, indexer.rs:380-386), and such a
+        # stale membership must keep reporting under the old id, not under whoever would reuse the slot.
+
+    def find_matches_batch(self, sequences: Sequence[Sequence[int]], early_exit: bool = False) -> List[OverlapScores]:
+        """Score many requests (each a list of LocalBlockHash) in one launch."""
+        lens = np.array([len(s) for s in sequences], dtype=np.int64)
+        offs = np.zeros(len(sequences) + 1, dtype=np.int64)
+        offs[1:] = np.cumsum(lens)
+        flat = np.zeros(max(int(offs[-1]), 1), dtype=np.uint64)
+        pos = 0
+        for s in sequences:
+            flat[pos:pos + len(s)] = np.asarray(s, dtype=np.uint64)
+            pos += len(s)
+        scores, _ = self.find_matches_device_arrays(flat, offs, early_exit)
+        return [self._to_overlap(row) for row in scores]
+
+    def find_matches(self, sequence: Sequence[int], early_exit: bool = False) -> OverlapScores:
+        """reference: indexer.rs:239-277 (one request)."""
+        return self.find_matches_batch([list(sequence)], early_exit)[0]
+
+    def find_matches_device_arrays(self, hashes: np.ndarray, seq_offsets: np.ndarray, early_exit: bool = False):
+        """Host arrays in, dense [n_req][MAX_WORKERS-in-use] scores out (slot order) plus matched depths."""
+        L = _lib.lib()
+        n_req = seq_offsets.size - 1
+        nw = max([s for s in self._slot.values()], default=-1) + 1
+        nw = max(nw, 1)
+        if n_req == 0:
+            return np.zeros((0, nw), dtype=np.uint32), np.zeros(0, dtype=np.int32)
+        hashes = np.ascontiguousarray(hashes, dtype=np.uint64)
+        seq_offsets = np.ascontiguousarray(seq_offsets, dtype=np.int64)
+        bufs = [C.c_void_p() for _ in range(4)]
+        sizes = [max(hashes.nbytes, 8), seq_offsets.nbytes, n_req * nw * 4, n_req * 4]
+        try:
+            for b, n in zip(bufs, sizes):
+                _lib.check(L.kvdp_device_alloc(C.byref(b), n, -1))
+            _lib.check(L.cuda_memcpy_sync(bufs[0], hashes.ctypes.data, hashes.nbytes))
+            _lib.check(L.cuda_memcpy_sync(bufs[1], seq_offsets.ctypes.data, seq_offsets.nbytes))
+            _lib.check(L.kvdp_index_find_matches(self._h, bufs[0], bufs[1], n_req, int(early_exit), nw, bufs[2], bufs[3],
+                                                 None))
+            stream = L.kvdp_index_stream(self._h)
+            scores = np.zeros((n_req, nw), dtype=np.uint32)
+            depth = np.zeros(n_req, dtype=np.int32)
+            _lib.check(L.cuda_memcpy_async(scores.ctypes.data, bufs[2], scores.nbytes, stream))
+            _lib.check(L.cuda_memcpy_async(depth.ctypes.data, bufs[3], depth.nbytes, stream))
+            _lib.check(L.kvdp_stream_synchronize(stream))
+        finally:
+            for b in bufs:
+                if b.value:
+                    L.kvdp_device_free(b)
+        return scores, depth
+
+    def _to_overlap(self, row: np.ndarray) -> OverlapScores:
+        out = OverlapScores()
+        for slot, c in enumerate(row):
+            if c and self._worker_of_slot[slot] is not None:
+                out.scores[self._worker_of_slot[slot]] = int(c)
+        return out
+
+    def stat(self, what: int, arg: int = 0) -> int:
+        return int(_lib.lib().kvdp_index_stat(self._h, what, arg))
+
+    def lookup_len(self, worker: WorkerId) -> int:
+        s = self._slot_of(worker, False)
+        return 0 if s is None else self.stat(2, s)
+
+    def close(self) -> None:
+        if self._h is not None and self._h.value:
+            _lib.lib().kvdp_index_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class KvIndexer:
+    """reference: KvIndexer (indexer.rs:498-667) without the tokio actor: same calls, synchronous."""
+
+    def __init__(self, kv_block_size: int, max_nodes: int = 1 << 20, device: int = -1):
+        self.kv_block_size = int(kv_block_size)
+        self.tree = RadixTree(max_nodes, device)
+
+    def block_size(self) -> int:
+        return self.kv_block_size
+
+    def apply_event(self, event: RouterEvent) -> None:
+        self.tree.apply_event(event)
+
+    def remove_worker(self, worker: WorkerId) -> None:
+        self.tree.remove_worker(worker)
+
+    def find_matches(self, sequence: Sequence[int]) -> OverlapScores:
+        return self.tree.find_matches(sequence, False)
+
+    def find_matches_for_request(self, tokens) -> OverlapScores:
+        """reference: indexer.rs:639-651 — hash the request's full blocks (seed 1337, un-chained), then match."""
+        return self.find_matches_for_requests([tokens])[0]
+
+    def find_matches_for_requests(self, requests: Sequence) -> List[OverlapScores]:
+        """Batched form: token lists in, one OverlapScores per request out; hashing and matching both on the GPU."""
+        from .tokens import hash_token_blocks
+        toks = [_as_u32(t) for t in requests]
+        offs = np.zeros(len(toks) + 1, dtype=np.int64)
+        offs[1:] = np.cumsum([t.size for t in toks])
+        flat = np.concatenate(toks) if toks else np.zeros(0, dtype=np.uint32)
+        boff, bh, _ = hash_token_blocks(flat, offs, self.kv_block_size, XXH3_SEED, chained=False)
+        scores, _ = self.tree.find_matches_device_arrays(bh if bh.size else np.zeros(1, dtype=np.uint64), boff, False)
+        return [self.tree._to_overlap(row) for row in scores]

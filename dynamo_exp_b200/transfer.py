@@ -227,6 +227,69 @@ class HostTier:
             pass
 
 
+# ---------------------------------------------------------------------------------------------- token-granular paths
+def reshape_and_cache(key_ptr: int, value_ptr: int, key_cache_ptr: int, value_cache_ptr: int, slot_mapping,
+                      num_slots: int, row_bytes: int, engine: Optional[TransferEngine] = None,
+                      device: int = -1) -> None:
+    """Token-granular paged write: `cache[slot_mapping[i]] = new[i]` for K and V in ONE launch — the data movement of
+    vLLM's `reshape_and_cache_flash`, which the reference's NCCL connector calls on every received layer
+    (container/deps/vllm/vllm_v0.8.4-dynamo-kv-disagg-patch.patch:1721-1746). `key`/`value` are `[num_tokens, H, D]`
+    contiguous, the caches `[num_blocks * block_size, H, D]` (flash layout viewed per slot), `row_bytes = H*D*elem`,
+    `slot = block * block_size + offset`; negative slots (padding) are skipped, as there."""
+    slots = np.asarray(slot_mapping, dtype=np.int64)
+    keep = np.nonzero(slots >= 0)[0]
+    if keep.size == 0:
+        return
+    if np.any(slots[keep] >= num_slots):
+        raise KvError("slot_mapping entry beyond the cache")
+    plan = CopyPlan.block_copy_raw([key_ptr, value_ptr], [key_cache_ptr, value_cache_ptr], 1, int(slots.size),
+                                   int(num_slots), int(row_bytes), 1, device)
+    own = engine is None
+    eng = engine or TransferEngine(int(keep.size), device)
+    try:
+        eng.run(plan, keep.astype(np.int32), slots[keep].astype(np.int32), num_layers=2)
+        eng.sync()
+    finally:
+        plan.close()
+        if own:
+            eng.close()
+
+
+def gather_token_rows(cache_ptr: int, out_ptr: int, slot_mapping, num_slots: int, row_bytes: int, col_offset: int = 0,
+                      col_bytes: Optional[int] = None, engine: Optional[TransferEngine] = None,
+                      device: int = -1) -> None:
+    """Token-granular gather with an optional head slice: `out[i] = cache[slot_mapping[i]][col_offset : +col_bytes]`,
+    what the reference's NCCL send path does per layer with torch indexing
+    (`cache.reshape(-1, H, D)[slot_mapping, h0:h1]`, patch:1602-1672). One launch, no intermediate tensor."""
+    slots = np.asarray(slot_mapping, dtype=np.int64)
+    if slots.size == 0:
+        return
+    if np.any(slots < 0) or np.any(slots >= num_slots):
+        raise KvError("slot_mapping entry outside the cache")
+    col_bytes = row_bytes - col_offset if col_bytes is None else col_bytes
+    if col_offset < 0 or col_bytes < 1 or col_offset + col_bytes > row_bytes:
+        raise KvError("column range outside the row")
+    src = np.array([cache_ptr], dtype=np.uint64)
+    dst = np.array([out_ptr], dtype=np.uint64)
+    d = _lib.PlanDesc()
+    d.num_layers, d.row_groups, d.prefix_dim, d.rows = 1, 1, 1, 1
+    d.run_bytes = col_bytes
+    d.src_block_stride, d.src_row_stride, d.src_col_offset = row_bytes, row_bytes, col_offset
+    d.dst_block_stride, d.dst_row_stride = col_bytes, col_bytes
+    d.src_blocks, d.dst_blocks = int(num_slots), int(slots.size)
+    d.src_layer_ptrs, d.dst_layer_ptrs, d.device = src.ctypes.data, dst.ctypes.data, device
+    plan = CopyPlan.from_desc(d, keepalive=(src, dst))
+    own = engine is None
+    eng = engine or TransferEngine(int(slots.size), device)
+    try:
+        eng.run(plan, slots.astype(np.int32), np.arange(slots.size, dtype=np.int32), num_layers=1)
+        eng.sync()
+    finally:
+        plan.close()
+        if own:
+            eng.close()
+
+
 # ---------------------------------------------------------------------------------------------- raw memory helpers
 def memcpy_sync(dst: int, src: int, nbytes: int) -> None:
     _lib.check(_lib.lib().cuda_memcpy_sync(C.c_void_p(dst), C.c_void_p(src), int(nbytes)))

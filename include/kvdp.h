@@ -193,6 +193,8 @@ int kvdp_xfer_sync(kvdp_xfer* x);
 /* Allocation-free launch on a caller stream with ids already resident on the device. */
 int kvdp_plan_launch(const kvdp_plan* plan, const int32_t* d_src_ids, const int32_t* d_dst_ids, int32_t num_pairs,
                      int32_t layer_begin, int32_t layer_end, kvdp_stream_t stream);
+/* Block the calling host thread until everything enqueued on `stream` has completed. */
+int kvdp_stream_synchronize(kvdp_stream_t stream);
 /* Make `stream` wait until *flag >= value (receiver side of kvdp_xfer_signal). */
 int kvdp_stream_wait_flag(kvdp_stream_t stream, uint32_t* flag, uint32_t value);
 
@@ -259,6 +261,35 @@ int kvdp_hash_token_blocks_host(const uint32_t* h_tokens, const int64_t* h_offse
  * that exercises every XXH3 length class. n strings of equal length `len`, packed; out[n]. */
 int kvdp_xxh3_64_batch(const uint8_t* d_data, int64_t n, int64_t len, uint64_t seed, uint64_t* d_out,
                        kvdp_stream_t stream);
+
+/* ---- prefix index: the KV router's RadixTree with batched GPU lookups (lib/llm/src/kv_router/indexer.rs:187-387) ----
+ * Events are applied on the host in call order (RadixTree::apply_event :284-378, remove_worker :380-386) and mirrored
+ * into device tables; find_matches (:239-277) runs for a whole batch of requests in one launch. Workers are slots
+ * 0..max_workers-1 (<= 64); the host layer maps the reference's i64 WorkerId to a slot. */
+typedef struct kvdp_index kvdp_index;
+int kvdp_index_create(kvdp_index** out, int64_t max_nodes, int32_t max_workers, int32_t device);
+int kvdp_index_destroy(kvdp_index* ix);
+kvdp_stream_t kvdp_index_stream(kvdp_index* ix);
+/* Stored event: blocks[i] = (block_hashes[i] = engine's ExternalSequenceBlockHash, tokens_hashes[i] = LocalBlockHash).
+ * Returns 0 on success, 1 when has_parent is set and this worker has no block `parent_hash` (the reference logs a
+ * warning and skips the event, :305-315), negative KVDP_E* on misuse or exhausted capacity. */
+int kvdp_index_apply_stored(kvdp_index* ix, int32_t worker, int32_t has_parent, uint64_t parent_hash,
+                            const uint64_t* block_hashes, const uint64_t* tokens_hashes, int32_t n);
+/* Removed event; unknown block hashes are skipped like in the reference (:354-364). */
+int kvdp_index_apply_removed(kvdp_index* ix, int32_t worker, const uint64_t* block_hashes, int32_t n);
+int kvdp_index_remove_worker(kvdp_index* ix, int32_t worker);
+/* Upload pending changes (find_matches does it implicitly). */
+int kvdp_index_flush(kvdp_index* ix);
+/* Requests are CSR sequences of LocalBlockHash in device memory (d_seq_offsets has n_req+1 entries). d_scores is
+ * [n_req][num_workers] u32 in worker-slot order: how many leading blocks of the request each worker holds;
+ * d_matched_depth[n_req] (optional) = number of blocks found in the tree. early_exit as in the reference: stop at the
+ * first block held by exactly one worker. Asynchronous on `stream` (NULL = the index's own stream). */
+int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int64_t* d_seq_offsets, int64_t n_req,
+                            int32_t early_exit, int32_t num_workers, uint32_t* d_scores, int32_t* d_matched_depth,
+                            kvdp_stream_t stream);
+/* Introspection for tests: what = 0 nodes; 1 children of node `arg`; 2 lookup entries of worker `arg`; 3 workers on node
+ * `arg`; 4 root's child for tokens hash `arg` (node id or -1); 5 workers with a lookup table. */
+int64_t kvdp_index_stat(kvdp_index* ix, int32_t what, uint64_t arg);
 
 #ifdef __cplusplus
 }

@@ -188,3 +188,38 @@ def test_rearrange_tensors_matches_the_triton_index_map(gpu, oracle, d, shape, e
         rearrange_tensors(d1.ptr, d2.ptr, shape, esz, 3, "write")
     with pytest.raises(KvError):
         rearrange_tensors(d1.ptr, d2.ptr, shape, esz, d, "sideways")
+
+
+@pytest.mark.parametrize("H,D,E", [(8, 128, 2), (4, 6, 4), (2, 3, 1)])
+def test_token_granular_paged_write_and_gather(gpu, H, D, E):
+    """slot_mapping scatter (reshape_and_cache_flash, patch:1721-1746) and the per-layer gather with a
+    head slice (patch:1602-1672), checked against numpy indexing."""
+    from dynamo_exp_b200.transfer import gather_token_rows, reshape_and_cache
+    rng = np.random.Generator(np.random.PCG64(H * D))
+    num_blocks, bs, ntok = 6, 4, 13
+    row = H * D * E
+    key = rng.integers(0, 255, size=(ntok, row), dtype=np.uint8)
+    val = rng.integers(0, 255, size=(ntok, row), dtype=np.uint8)
+    slots = rng.permutation(num_blocks * bs)[:ntok].astype(np.int64)
+    slots[3] = -1                                              # padding token: skipped
+    dk, dv = DevBuf(gpu, key.nbytes), DevBuf(gpu, val.nbytes)
+    ck, cv = DevBuf(gpu, num_blocks * bs * row), DevBuf(gpu, num_blocks * bs * row)
+    dk.upload(key)
+    dv.upload(val)
+    reshape_and_cache(dk.ptr, dv.ptr, ck.ptr, cv.ptr, slots, num_blocks * bs, row)
+    want_k = np.zeros((num_blocks * bs, row), dtype=np.uint8)
+    want_v = np.zeros_like(want_k)
+    ok = slots >= 0
+    want_k[slots[ok]] = key[ok]
+    want_v[slots[ok]] = val[ok]
+    assert np.array_equal(ck.download().reshape(-1, row), want_k)
+    assert np.array_equal(cv.download().reshape(-1, row), want_v)
+    # gather heads [h0, h1) of the written tokens back out: cache.reshape(-1, H, D)[slots, h0:h1]
+    h0, h1 = (H // 2, H) if H > 1 else (0, 1)
+    sel = slots[ok]
+    out = DevBuf(gpu, sel.size * (h1 - h0) * D * E)
+    gather_token_rows(ck.ptr, out.ptr, sel, num_blocks * bs, row, h0 * D * E, (h1 - h0) * D * E)
+    want = want_k.reshape(-1, H, D * E)[sel, h0:h1].reshape(sel.size, -1)
+    assert np.array_equal(out.download().reshape(sel.size, -1), want)
+    with pytest.raises(KvError):
+        gather_token_rows(ck.ptr, out.ptr, [num_blocks * bs], num_blocks * bs, row)

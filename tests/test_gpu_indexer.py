@@ -1,0 +1,181 @@
+"""GPU: the prefix index (RadixTree / KvIndexer mirror over kvdp_index_*). Parity against the CPU oracle
+(oracle/radix_oracle.py, itself pinned to the reference's unit tests) on the reference's own scenarios and on random
+event streams with sharing, removals, worker removal and early exit; wire-format tests follow protocols.rs:160-250."""
+import json
+
+import numpy as np
+import pytest
+
+from dynamo_exp_b200.indexer import (KvCacheEvent, KvCacheEvents, KvCacheRemoveData, KvCacheStoreData,
+                                     KvCacheStoredBlockData, KvIndexer, RadixTree, RouterEvent)
+from oracle.radix_oracle import RadixTree as OracleTree
+from tests.util import tokens_for
+
+pytestmark = pytest.mark.gpu
+
+
+def store_event(worker, event_id, hashes, parent=None):
+    # make_blocks (indexer.rs:900-908): tokens_hash = i, block_hash = i * 100
+    return RouterEvent(worker, KvCacheEvent(event_id, KvCacheStoreData(
+        parent, [KvCacheStoredBlockData(i * 100, i) for i in hashes])))
+
+
+def remove_event(worker, event_id, hashes):
+    return RouterEvent(worker, KvCacheEvent(event_id, KvCacheRemoveData([i * 100 for i in hashes])))
+
+
+def root_child(trie, tokens_hash):
+    return trie.stat(4, tokens_hash)
+
+
+def test_radix_tree_reference_scenario(gpu):
+    """indexer.rs:949-1150, assertion for assertion (lookup sizes, root child's workers/children, shared block)."""
+    trie = RadixTree(max_nodes=1024)
+    w1, w2 = 0, 1
+    trie.apply_event(store_event(w1, 1, [1, 2, 3]))
+    assert trie.find_matches([1, 2, 3], False).scores[w1] == 3
+    assert trie.stat(5) == 1 and trie.lookup_len(w1) == 3
+    assert trie.stat(3, 0) == 0 and trie.stat(1, 0) == 1
+    c = root_child(trie, 1)
+    assert trie.stat(3, c) == 1 and trie.stat(1, c) == 1
+    trie.apply_event(store_event(w2, 1, [1, 4, 5]))
+    s = trie.find_matches([1, 2, 3], False).scores
+    assert s[w1] == 3 and s[w2] == 1
+    assert trie.stat(5) == 2 and trie.lookup_len(w1) == 3 and trie.lookup_len(w2) == 3
+    assert trie.stat(3, c) == 2 and trie.stat(1, c) == 2
+    trie.apply_event(remove_event(w2, 2, [5]))
+    assert trie.lookup_len(w1) == 3 and trie.lookup_len(w2) == 2
+    assert trie.stat(3, c) == 2 and trie.stat(1, c) == 2
+    trie.apply_event(remove_event(w2, 3, [4]))
+    assert trie.lookup_len(w2) == 1 and trie.stat(3, c) == 2 and trie.stat(1, c) == 2
+    trie.apply_event(store_event(w2, 4, [2, 6, 7], parent=100))
+    s = trie.find_matches([1, 2, 3], False).scores
+    assert s[w1] == 3 and s[w2] == 2
+    assert trie.lookup_len(w1) == 3 and trie.lookup_len(w2) == 4
+    assert trie.stat(3, c) == 2 and trie.stat(1, c) == 2
+    trie.close()
+
+
+def test_remove_worker_and_early_stopping_reference_scenarios(gpu):
+    trie = RadixTree(max_nodes=256)       # indexer.rs:1152-1175
+    assert trie.find_matches([0], False).scores == {}
+    trie.apply_event(store_event(0, 0, [0]))
+    trie.apply_event(store_event(1, 0, [0]))
+    assert trie.find_matches([0], False).scores == {0: 1, 1: 1}
+    trie.remove_worker(0)
+    assert trie.find_matches([0], False).scores == {1: 1}
+    trie.close()
+    trie = RadixTree(max_nodes=256)       # indexer.rs:1177-1200
+    trie.apply_event(store_event(0, 0, [0, 1, 2]))
+    trie.apply_event(store_event(1, 0, [0]))
+    assert trie.find_matches([0, 1, 2], True).scores == {0: 2, 1: 1}
+    assert trie.find_matches([0, 1], True).scores == {0: 2, 1: 1}
+    assert trie.find_matches([0, 1, 2], False).scores == {0: 3, 1: 1}
+    trie.close()
+
+
+def test_unknown_parent_and_cleared_children(gpu):
+    trie = RadixTree(max_nodes=256)
+    trie.apply_event(store_event(0, 0, [1, 2], parent=999))         # skipped: unknown parent
+    assert trie.find_matches([1, 2], False).scores == {}
+    trie.apply_event(remove_event(0, 1, [42]))                       # ignored
+    trie.apply_event(store_event(0, 2, [1, 2]))
+    trie.apply_event(remove_event(0, 3, [1]))                        # last worker leaves block 1 -> children dropped
+    assert trie.find_matches([1, 2], False).scores == {}
+    trie.apply_event(store_event(0, 4, [1, 9]))                      # re-populating the emptied block works
+    assert trie.find_matches([1, 9], False).scores == {0: 2}
+    assert trie.find_matches([1, 2], False).scores == {0: 1}         # the old edge 1->2 must stay dead
+    trie.close()
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_random_event_streams_match_the_oracle(gpu, seed):
+    """Random stores (fresh, extending, sharing engine block ids across parents), removes, worker removals; after every
+    few events a batch of random queries is scored on the GPU and by the oracle, early_exit on and off."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    trie, ora = RadixTree(max_nodes=1 << 14), OracleTree()
+    workers = [10, -3, 7, 2 ** 40, 5]
+    vocab = 12                          # small alphabet -> lots of shared prefixes
+    stored = {w: [] for w in workers}   # (external hash, tokens hash) chains this worker has stored
+    next_ext = [1000]
+
+    def queries():
+        qs = [list(rng.integers(0, vocab, size=int(rng.integers(0, 9)))) for _ in range(40)]
+        for early in (False, True):
+            got = trie.find_matches_batch(qs, early)
+            for q, g in zip(qs, got):
+                assert g.scores == ora.find_matches([int(x) for x in q], early), (q, early)
+
+    for step in range(160):
+        w = workers[int(rng.integers(len(workers)))]
+        op = rng.random()
+        if op < 0.6:
+            n = int(rng.integers(1, 5))
+            parent = None
+            if stored[w] and rng.random() < 0.6:
+                parent = stored[w][int(rng.integers(len(stored[w])))][0]
+            blocks = []
+            for _ in range(n):
+                if stored[w] and rng.random() < 0.15:        # reuse an engine block id under a new parent (sharing)
+                    ext = stored[w][int(rng.integers(len(stored[w])))][0]
+                else:
+                    ext = next_ext[0]
+                    next_ext[0] += 1
+                blocks.append((ext, int(rng.integers(vocab))))
+            if rng.random() < 0.05:
+                parent = 987654321                            # unknown parent: both sides must skip the event
+            ev = RouterEvent(w, KvCacheEvent(step, KvCacheStoreData(
+                parent, [KvCacheStoredBlockData(e, t) for e, t in blocks])))
+            trie.apply_event(ev)
+            if ora.apply_stored(w, parent, blocks):
+                stored[w] += blocks
+        elif op < 0.9:
+            if stored[w]:
+                k = int(rng.integers(1, 4))
+                victims = [stored[w][int(rng.integers(len(stored[w])))][0] for _ in range(k)] + [31337]
+                trie.apply_event(RouterEvent(w, KvCacheEvent(step, KvCacheRemoveData(victims))))
+                ora.apply_removed(w, victims)
+                stored[w] = [b for b in stored[w] if b[0] not in victims]
+        else:
+            trie.remove_worker(w)
+            ora.remove_worker(w)
+            stored[w] = []
+        if step % 8 == 7:
+            queries()
+    queries()
+    trie.close()
+
+
+def test_find_matches_for_request_hashes_on_the_gpu(gpu, oracle):
+    """indexer.rs:639-651 + the sharded/actor tests' shape (block sizes 11/32/64): tokens in, scores out."""
+    for bs in (11, 32, 64):
+        idx = KvIndexer(bs, max_nodes=4096)
+        toks = tokens_for(1, 5 * bs + 3)
+        hashes = [int(x) for x in oracle.indexer_block_hashes(toks, bs)]
+        idx.apply_event(RouterEvent(0, KvCacheEvent(1, KvCacheStoreData(None, [
+            KvCacheStoredBlockData(1000 + i, h) for i, h in enumerate(hashes[:4])]))))
+        idx.apply_event(RouterEvent(1, KvCacheEvent(1, KvCacheStoreData(None, [
+            KvCacheStoredBlockData(2000 + i, h) for i, h in enumerate(hashes[:2])]))))
+        assert idx.find_matches_for_request(toks).scores == {0: 4, 1: 2}
+        assert idx.find_matches(hashes).scores == {0: 4, 1: 2}
+        other = tokens_for(2, 3 * bs)
+        out = idx.find_matches_for_requests([toks, other, toks[:bs - 1], toks[:2 * bs]])
+        assert [o.scores for o in out] == [{0: 4, 1: 2}, {}, {}, {0: 2, 1: 2}]
+        idx.tree.close()
+
+
+def test_router_event_wire_format(gpu):
+    """protocols.rs:160-250 and the serde derives: snake_case variant keys, hashes as bare u64 numbers."""
+    ev = RouterEvent(7, KvCacheEvent(1, KvCacheStoreData(1, [KvCacheStoredBlockData(2, 3)])))
+    assert ev.to_json() == ('{"worker_id":7,"event":{"event_id":1,"data":{"stored":{"parent_hash":1,'
+                            '"blocks":[{"block_hash":2,"tokens_hash":3}]}}}}')
+    assert RouterEvent.from_json(ev.to_json()) == ev
+    rm = RouterEvent(-2, KvCacheEvent(9, KvCacheRemoveData([4, 5])))
+    assert json.loads(rm.to_json())["event"]["data"] == {"removed": {"block_hashes": [4, 5]}}
+    assert RouterEvent.from_json(rm.to_json()) == rm
+    evs = KvCacheEvents([ev.event], False)
+    back = KvCacheEvents.from_json(evs.to_json())
+    assert len(back.events) == 1 and back.events[0].data.parent_hash == 1 and not back.shutdown
+    assert back.events[0].data.blocks[0].block_hash == 2 and back.events[0].data.blocks[0].tokens_hash == 3
+    big = RouterEvent(1, KvCacheEvent(2 ** 63, KvCacheStoreData(None, [KvCacheStoredBlockData(2 ** 64 - 1, 2 ** 63 + 5)])))
+    assert RouterEvent.from_json(big.to_json()) == big
