@@ -264,6 +264,77 @@ def host_tier_bench(torch, lib):
             "staging": "2 x 32 blocks (2 x 256 MiB HBM), one DMA per request range, gather/scatter kernel per slot"}
 
 
+def router_index_bench(torch, lib, steps=10):
+    """the router's prefix index. 8 workers hold prefixes of 256 synthetic documents; 57 344 requests
+    (ISL 512..32k -> 8..512 block hashes each) share a document prefix of random length and then diverge. One launch
+    scores the whole batch (RadixTree::find_matches, indexer.rs:239-277)."""
+    L = lib.lib()
+    rng = np.random.Generator(np.random.PCG64(2024))
+    n_workers, n_docs, doc_blocks = 8, 256, 512
+
+    def doc_hash(d, j):
+        x = (np.uint64(d) << np.uint64(32)) | np.asarray(j, dtype=np.uint64)
+        x = (x + np.uint64(0x9E3779B97F4A7C15)) * np.uint64(0xBF58476D1CE4E5B9)
+        return x ^ (x >> np.uint64(31))
+    ix = C.c_void_p()
+    lib.check(L.kvdp_index_create(C.byref(ix), 1 << 20, 64, 0))
+    t0 = time.perf_counter()
+    events = 0
+    with np.errstate(over="ignore"):
+        for w in range(n_workers):
+            for d in rng.permutation(n_docs)[:n_docs // 2]:
+                depth = int(rng.integers(16, doc_blocks + 1))
+                th = doc_hash(d, np.arange(depth))
+                bh = th ^ np.uint64(w + 1)              # engine-side ids: distinct per worker
+                lib.check(L.kvdp_index_apply_stored(ix, w, 0, 0, bh.ctypes.data, th.ctypes.data, depth))
+                events += 1
+    lib.check(L.kvdp_index_flush(ix))
+    build_s = time.perf_counter() - t0
+    isl_blocks = [8, 16, 32, 64, 128, 256, 512]
+    n_req = 7 * 8192
+    lens = np.array([isl_blocks[i % 7] for i in range(n_req)], dtype=np.int64)
+    offs = np.zeros(n_req + 1, dtype=np.int64)
+    offs[1:] = np.cumsum(lens)
+    total = int(offs[-1])
+    seqs = np.empty(total, dtype=np.uint64)
+    docs = rng.integers(0, n_docs, size=n_req)
+    share = (rng.random(n_req) * (lens + 1)).astype(np.int64)      # blocks shared with the document
+    with np.errstate(over="ignore"):
+        for r in range(n_req):
+            n, k = int(lens[r]), int(share[r])
+            seqs[offs[r]:offs[r] + k] = doc_hash(docs[r], np.arange(k))
+            seqs[offs[r] + k:offs[r] + n] = doc_hash(1 << 20 | r, np.arange(n - k))
+    d_seq = torch.from_numpy(seqs.view(np.int64)).cuda()
+    d_off = torch.from_numpy(offs).cuda()
+    d_scores = torch.zeros(n_req * n_workers, dtype=torch.int32, device="cuda")
+    d_depth = torch.zeros(n_req, dtype=torch.int32, device="cuda")
+    st = torch.cuda.Stream()     # an explicit stream: NULL would select the index's own stream
+
+    def run():
+        lib.check(L.kvdp_index_find_matches(ix, d_seq.data_ptr(), d_off.data_ptr(), n_req, 0, n_workers,
+                                            d_scores.data_ptr(), d_depth.data_ptr(), C.c_void_p(st.cuda_stream)))
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(st)
+    for _ in range(steps):
+        run()
+    b.record(st)
+    torch.cuda.synchronize()
+    sec = a.elapsed_time(b) / 1e3 / steps
+    depth = d_depth.cpu().numpy()
+    probes = int(depth.sum()) + int((depth < lens).sum())          # matched steps + the miss that ends a walk
+    nodes = int(L.kvdp_index_stat(ix, 0, 0))
+    L.kvdp_index_destroy(ix)
+    return {"requests_per_s": n_req / sec, "ms_per_batch": sec * 1e3, "requests": n_req, "workers": n_workers,
+            "tree_nodes": nodes, "store_events": events, "tree_build_s": build_s,
+            "avg_matched_blocks": float(depth.mean()), "probes_per_s": probes / sec,
+            "bytes_per_probe": 32, "random_access_GBps": probes * 32 / sec / GB,
+            "note": "one thread per request; each step = ONE dependent 32-byte random read (edge record carrying the "
+                    "child's worker set); latency-bound on the longest walk (512 blocks), not bandwidth-bound"}
+
+
 def hash_bench(torch, lib, steps, warmup, peak):
     """Router-sweep shaped batch (ISL 512..32k round-robin, 64-token blocks) resident in HBM; chained + block hashes."""
     from tests.util import mix64
@@ -417,6 +488,7 @@ def run_single(args):
     if not args.no_hash:
         line["hash"] = hash_bench(torch, lib, 10, 3, peak)
         line["hashes_per_s"] = line["hash"]["hashes_per_s"]
+        line["router_index"] = router_index_bench(torch, lib)
     if not args.no_cpu:
         from oracle import kvoracle as ko
         threads = ko.hw_threads()

@@ -10,11 +10,11 @@
 //   * event application stays on the host, serial and in event order (it IS order-dependent), in a plain C++ mirror of
 //     the reference's semantics — including blocks shared between parents through the per-worker table and the
 //     "last worker left: drop all children" rule;
-//   * every change is mirrored into two flat device arrays: node records {worker bitset, generation} and an
-//     open-addressing edge table keyed by (parent node, parent generation, tokens hash) -> child node. Dropping a
-//     node's children is a generation bump (stale edges simply stop matching);
-//   * find_matches runs for a whole batch of requests in one launch, one thread per request, each step one 32-byte
-//     edge probe + one 16-byte node read; per-worker scores are kept as bit-sliced counters (one 64-bit plane per
+//   * every change is mirrored into ONE flat device array: an open-addressing edge table keyed by (parent node, parent
+//     generation, tokens hash) whose 32-byte records also carry the child's id, worker bitset and generation.
+//     Dropping a node's children is a generation bump (stale edges simply stop matching);
+//   * find_matches runs for a whole batch of requests in one launch, one thread per request, each step ONE 32-byte
+//     dependent random read; per-worker scores are kept as bit-sliced counters (one 64-bit plane per
 //     binary digit), so adding a node's worker set costs a ripple of AND/XORs instead of a 64-way loop.
 // Up to 64 workers per index (one bitset word); the host layer maps WorkerId -> slot.
 #include <string.h>
@@ -28,18 +28,16 @@
 namespace kvdp {
 namespace {
 
-struct NodeRec {   // 16 bytes
-  uint64_t workers;
-  uint32_t gen;
-  uint32_t pad;
-};
-struct EdgeRec {   // 32 bytes: one sector per probe
+// 32 bytes = one sector per probe. The child's worker set and generation ride along in the edge, so a walk step is
+// ONE dependent random read instead of two (edge, then node record); the host rewrites the copies whenever a node's
+// set or generation changes (it keeps, per node, the table slots of its incoming edges).
+struct EdgeRec {
   uint64_t hash;
   uint32_t parent;
-  uint32_t gen;
+  uint32_t gen;            // parent's generation when the edge was inserted
+  uint64_t child_workers;
   uint32_t child;
-  uint32_t used;
-  uint64_t pad;
+  uint32_t child_gen1;     // child's generation + 1; 0 marks an empty slot
 };
 
 __host__ __device__ __forceinline__ uint64_t edge_slot_hash(uint64_t hash, uint32_t parent, uint32_t gen) {
@@ -52,8 +50,8 @@ __host__ __device__ __forceinline__ uint64_t edge_slot_hash(uint64_t hash, uint3
 
 constexpr int kPlanes = 16;  // bit-sliced counters: depths up to 65535 blocks
 
-__global__ void __launch_bounds__(128) kvdp_index_find_kernel(const NodeRec* __restrict__ nodes,
-                                                              const EdgeRec* __restrict__ edges, uint64_t mask,
+__global__ void __launch_bounds__(128) kvdp_index_find_kernel(const EdgeRec* __restrict__ edges, uint64_t mask,
+                                                              uint32_t root_gen,
                                                               const uint64_t* __restrict__ hashes,
                                                               const int64_t* __restrict__ seq_offsets, int64_t n_req,
                                                               int early_exit, int num_workers,
@@ -65,26 +63,26 @@ __global__ void __launch_bounds__(128) kvdp_index_find_kernel(const NodeRec* __r
   uint64_t plane[kPlanes];
 #pragma unroll
   for (int p = 0; p < kPlanes; ++p) plane[p] = 0;
-  uint32_t node = 0, gen = nodes[0].gen;
+  uint32_t node = 0, gen = root_gen;
   int depth = 0;
   for (int64_t i = s0; i < s1; ++i) {
     const uint64_t h = __ldg(hashes + i);
     uint64_t slot = edge_slot_hash(h, node, gen) & mask;
-    uint32_t child = 0xffffffffu;
+    bool found = false;
+    uint4 a, b;
     for (;;) {
-      const uint4 a = __ldg(reinterpret_cast<const uint4*>(edges + slot));       // hash, parent, gen
-      const uint2 b = __ldg(reinterpret_cast<const uint2*>(edges + slot) + 2);   // child, used
-      if (b.y == 0) break;                                                        // empty slot: not present
+      a = __ldg(reinterpret_cast<const uint4*>(edges + slot));       // hash, parent, gen
+      b = __ldg(reinterpret_cast<const uint4*>(edges + slot) + 1);   // child_workers, child, child_gen + 1
+      if (b.w == 0) break;                                            // empty slot: not present
       const uint64_t eh = (uint64_t)a.x | ((uint64_t)a.y << 32);
       if (eh == h && a.z == node && a.w == gen) {
-        child = b.x;
+        found = true;
         break;
       }
       slot = (slot + 1) & mask;
     }
-    if (child == 0xffffffffu) break;
-    const uint4 nr = __ldg(reinterpret_cast<const uint4*>(nodes + child));
-    uint64_t carry = (uint64_t)nr.x | ((uint64_t)nr.y << 32);
+    if (!found) break;
+    uint64_t carry = (uint64_t)b.x | ((uint64_t)b.y << 32);
     const int nworkers = __popcll(carry);
     ++depth;
 #pragma unroll
@@ -94,8 +92,8 @@ __global__ void __launch_bounds__(128) kvdp_index_find_kernel(const NodeRec* __r
       carry = t;
     }
     if (early_exit && nworkers == 1) break;
-    node = child;
-    gen = nr.z;
+    node = b.z;
+    gen = b.w - 1;
   }
   if (matched_depth) matched_depth[r] = depth;
   for (int w = 0; w < num_workers; ++w) {
@@ -115,6 +113,7 @@ __global__ void kvdp_index_scatter_kernel(Rec* __restrict__ table, const uint32_
 
 struct HostNode {
   std::unordered_map<uint64_t, uint32_t> children;  // tokens hash -> node id
+  std::vector<uint32_t> in_slots;                    // edge-table slots of edges that point at this node
   uint64_t workers = 0;
   uint32_t gen = 0;
 };
@@ -134,10 +133,9 @@ struct kvdp_index {
   std::unordered_map<uint64_t, uint32_t> lookup[64];
   bool lookup_present[64] = {};
   std::vector<EdgeRec> h_edges;
-  NodeRec* d_nodes = nullptr;
   EdgeRec* d_edges = nullptr;
-  std::vector<uint32_t> dirty_nodes, dirty_edges;
-  std::vector<uint8_t> node_dirty_flag, edge_dirty_flag;
+  std::vector<uint32_t> dirty_edges;
+  std::vector<uint8_t> edge_dirty_flag;
   // upload staging (grown on demand)
   uint32_t* d_idx = nullptr;
   void* d_recs = nullptr;
@@ -148,10 +146,23 @@ struct kvdp_index {
 
 namespace {
 
+void mark_edge(kvdp_index* ix, uint64_t slot) {
+  if (!ix->edge_dirty_flag[slot]) {
+    ix->edge_dirty_flag[slot] = 1;
+    ix->dirty_edges.push_back((uint32_t)slot);
+  }
+}
+
+// A node's worker set or generation changed: refresh the copies carried by its incoming edges.
 void mark_node(kvdp_index* ix, uint32_t n) {
-  if (!ix->node_dirty_flag[n]) {
-    ix->node_dirty_flag[n] = 1;
-    ix->dirty_nodes.push_back(n);
+  const HostNode& h = ix->nodes[n];
+  for (uint32_t slot : h.in_slots) {
+    EdgeRec& e = ix->h_edges[slot];
+    if (e.child_gen1 != 0 && e.child == n) {
+      e.child_workers = h.workers;
+      e.child_gen1 = h.gen + 1;
+      mark_edge(ix, slot);
+    }
   }
 }
 
@@ -161,17 +172,16 @@ int insert_edge(kvdp_index* ix, uint32_t parent, uint64_t hash, uint32_t child) 
   uint64_t slot = edge_slot_hash(hash, parent, gen) & mask;
   for (uint64_t probes = 0; probes < ix->capacity; ++probes) {
     EdgeRec& e = ix->h_edges[slot];
-    if (!e.used) {
+    if (e.child_gen1 == 0) {
       e.hash = hash;
       e.parent = parent;
       e.gen = gen;
       e.child = child;
-      e.used = 1;
+      e.child_workers = ix->nodes[child].workers;
+      e.child_gen1 = ix->nodes[child].gen + 1;
       ++ix->live_slots;
-      if (!ix->edge_dirty_flag[slot]) {
-        ix->edge_dirty_flag[slot] = 1;
-        ix->dirty_edges.push_back((uint32_t)slot);
-      }
+      ix->nodes[child].in_slots.push_back((uint32_t)slot);
+      mark_edge(ix, slot);
       return 0;
     }
     slot = (slot + 1) & mask;
@@ -185,6 +195,7 @@ int rebuild_edges(kvdp_index* ix) {
   std::fill(ix->edge_dirty_flag.begin(), ix->edge_dirty_flag.end(), 0);
   ix->dirty_edges.clear();
   ix->live_slots = 0;
+  for (auto& n : ix->nodes) n.in_slots.clear();
   for (uint32_t p = 0; p < ix->nodes.size(); ++p)
     for (auto& kv : ix->nodes[p].children)
       if (int rc = insert_edge(ix, p, kv.first, kv.second)) return rc;
@@ -197,7 +208,6 @@ int new_node(kvdp_index* ix, uint32_t* out) {
     return fail(KVDP_ERANGE, "prefix index: node capacity %lld exhausted", (long long)ix->max_nodes);
   ix->nodes.emplace_back();
   *out = (uint32_t)ix->nodes.size() - 1;
-  mark_node(ix, *out);
   return 0;
 }
 
@@ -234,14 +244,11 @@ int kvdp_index_create(kvdp_index** out, int64_t max_nodes, int32_t max_workers, 
   ix->capacity = cap;
   ix->h_edges.assign(cap, EdgeRec{});
   ix->edge_dirty_flag.assign(cap, 0);
-  ix->node_dirty_flag.assign((size_t)max_nodes, 0);
   ix->nodes.reserve((size_t)std::min<int64_t>(max_nodes, 1 << 20));
   ix->nodes.emplace_back();  // root
   DeviceGuard g(ix->device);
   cudaError_t e = cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking);
-  if (e == cudaSuccess) e = cudaMalloc(&ix->d_nodes, sizeof(NodeRec) * (size_t)max_nodes);
   if (e == cudaSuccess) e = cudaMalloc(&ix->d_edges, sizeof(EdgeRec) * cap);
-  if (e == cudaSuccess) e = cudaMemset(ix->d_nodes, 0, sizeof(NodeRec) * (size_t)max_nodes);
   if (e == cudaSuccess) e = cudaMemset(ix->d_edges, 0, sizeof(EdgeRec) * cap);
   if (e != cudaSuccess) {
     kvdp_index_destroy(ix);
@@ -259,7 +266,6 @@ int kvdp_index_destroy(kvdp_index* ix) {
     cudaStreamSynchronize(ix->stream);
     cudaStreamDestroy(ix->stream);
   }
-  if (ix->d_nodes) cudaFree(ix->d_nodes);
   if (ix->d_edges) cudaFree(ix->d_edges);
   if (ix->d_idx) cudaFree(ix->d_idx);
   if (ix->d_recs) cudaFree(ix->d_recs);
@@ -363,34 +369,18 @@ int kvdp_index_flush(kvdp_index* ix) {
     ix->dirty_edges.clear();
     ix->full_upload_needed = false;
   }
-  const size_t ne = ix->dirty_edges.size(), nn = ix->dirty_nodes.size();
-  if (ne == 0 && nn == 0) return 0;
-  if (int rc = ensure_stage(ix, std::max(ne, nn))) return rc;
-  if (ne) {
-    std::vector<EdgeRec> recs(ne);
-    for (size_t i = 0; i < ne; ++i) recs[i] = ix->h_edges[ix->dirty_edges[i]];
-    KVDP_CUDA(cudaMemcpyAsync(ix->d_idx, ix->dirty_edges.data(), ne * sizeof(uint32_t), cudaMemcpyHostToDevice, ix->stream));
-    KVDP_CUDA(cudaMemcpyAsync(ix->d_recs, recs.data(), ne * sizeof(EdgeRec), cudaMemcpyHostToDevice, ix->stream));
-    kvdp_index_scatter_kernel<EdgeRec><<<(unsigned)((ne + 255) / 256), 256, 0, ix->stream>>>(
-        ix->d_edges, ix->d_idx, (const EdgeRec*)ix->d_recs, (int)ne);
-    KVDP_CUDA(cudaStreamSynchronize(ix->stream));
-    for (uint32_t s : ix->dirty_edges) ix->edge_dirty_flag[s] = 0;
-    ix->dirty_edges.clear();
-  }
-  if (nn) {
-    std::vector<NodeRec> recs(nn);
-    for (size_t i = 0; i < nn; ++i) {
-      const HostNode& h = ix->nodes[ix->dirty_nodes[i]];
-      recs[i] = NodeRec{h.workers, h.gen, 0};
-    }
-    KVDP_CUDA(cudaMemcpyAsync(ix->d_idx, ix->dirty_nodes.data(), nn * sizeof(uint32_t), cudaMemcpyHostToDevice, ix->stream));
-    KVDP_CUDA(cudaMemcpyAsync(ix->d_recs, recs.data(), nn * sizeof(NodeRec), cudaMemcpyHostToDevice, ix->stream));
-    kvdp_index_scatter_kernel<NodeRec><<<(unsigned)((nn + 255) / 256), 256, 0, ix->stream>>>(
-        ix->d_nodes, ix->d_idx, (const NodeRec*)ix->d_recs, (int)nn);
-    KVDP_CUDA(cudaStreamSynchronize(ix->stream));
-    for (uint32_t n : ix->dirty_nodes) ix->node_dirty_flag[n] = 0;
-    ix->dirty_nodes.clear();
-  }
+  const size_t ne = ix->dirty_edges.size();
+  if (ne == 0) return 0;
+  if (int rc = ensure_stage(ix, ne)) return rc;
+  std::vector<EdgeRec> recs(ne);
+  for (size_t i = 0; i < ne; ++i) recs[i] = ix->h_edges[ix->dirty_edges[i]];
+  KVDP_CUDA(cudaMemcpyAsync(ix->d_idx, ix->dirty_edges.data(), ne * sizeof(uint32_t), cudaMemcpyHostToDevice, ix->stream));
+  KVDP_CUDA(cudaMemcpyAsync(ix->d_recs, recs.data(), ne * sizeof(EdgeRec), cudaMemcpyHostToDevice, ix->stream));
+  kvdp_index_scatter_kernel<EdgeRec><<<(unsigned)((ne + 255) / 256), 256, 0, ix->stream>>>(
+      ix->d_edges, ix->d_idx, (const EdgeRec*)ix->d_recs, (int)ne);
+  KVDP_CUDA(cudaStreamSynchronize(ix->stream));
+  for (uint32_t s : ix->dirty_edges) ix->edge_dirty_flag[s] = 0;
+  ix->dirty_edges.clear();
   KVDP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -410,7 +400,7 @@ int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int6
   DeviceGuard g(ix->device);
   cudaStream_t stream = stream_ ? (cudaStream_t)stream_ : ix->stream;
   kvdp_index_find_kernel<<<(unsigned)((n_req + 127) / 128), 128, 0, stream>>>(
-      ix->d_nodes, ix->d_edges, ix->capacity - 1, d_hashes, d_seq_offsets, n_req, early_exit, num_workers, d_scores,
+      ix->d_edges, ix->capacity - 1, ix->nodes[0].gen, d_hashes, d_seq_offsets, n_req, early_exit, num_workers, d_scores,
       d_matched_depth);
   KVDP_CUDA(cudaGetLastError());
   return 0;
