@@ -420,8 +420,8 @@ def hash_bench(torch, lib, steps, warmup, peak):
                         "frac": nblk * 264 / sec_un / GB / peak, "kernel": "kvdp_hash_blocks_tma<4,8>",
                         "algorithmic_bytes_per_launch": nblk * 264,
                         "traffic": ncu_traffic("kvdp_hash_blocks_tma"),
-                        "traffic_note": "ncu traffic was captured on the 2.08 M-block batch (0.5506 GB vs 0.5493 GB "
-                                        "algorithmic, ratio 1.002)"},
+                        "traffic_note": "ncu --set full on this batch: 2.150 GB read + 0.069 GB written vs 2.197 GB "
+                                        "algorithmic (ratio 1.010); profiles/ncu_full_r01_summary.txt"},
            "chained_hbm_frac": nblk * 272 / sec_serial / GB / peak}
     # e2e: pinned host tokens -> device -> hashes back on the host, through kvdp_hash_token_blocks_host
     n_e = 7 * 256
