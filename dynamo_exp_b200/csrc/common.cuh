@@ -29,8 +29,9 @@ struct Options {
   int64_t tile_bytes = 0;   // 0 = default per path
   int64_t stages = 0;       // 0 = default per path
   int64_t ctas_per_sm = 0;  // 0 = default per path
-  int64_t host_path = 0;    // 0 kernel zero-copy for pinned host memory, 1 per-chunk DMA loop
+  int64_t host_path = 0;    // pinned host memory: 0 vector kernel (zero-copy), 1 per-chunk DMA loop, 2 TMA kernel
   int64_t host_ctas = 0;    // CTAs used when one side is host memory (0 = default)
+  int64_t l2_hint = 0;      // path 3: 1 = evict_first on loads, 2 = on stores, 3 = both
 };
 Options& options();
 
@@ -116,6 +117,25 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void* src_gmem
 }
 __device__ __forceinline__ void bulk_s2g(void* dst_gmem, uint32_t src_smem, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(src_smem), "r"(bytes)
+               : "memory");
+}
+// Same copies with an L2 eviction-priority hint (streaming data that will not be re-read soon)
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(uint32_t dst_smem, const void* src_gmem, uint32_t bytes, uint32_t bar,
+                                              uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          dst_smem),
+      "l"(src_gmem), "r"(bytes), "r"(bar), "l"(pol)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_s2g_hint(void* dst_gmem, uint32_t src_smem, uint32_t bytes, uint64_t pol) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst_gmem),
+               "r"(src_smem), "r"(bytes), "l"(pol)
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }

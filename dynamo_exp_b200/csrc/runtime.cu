@@ -87,8 +87,11 @@ int kvdp_set_option(const char* name, int64_t value) {
     if (value < 0 || value > 32) return fail(KVDP_EINVAL, "ctas_per_sm must be 0..32");
     o.ctas_per_sm = value;
   } else if (!strcmp(name, "host_path")) {
-    if (value < 0 || value > 1) return fail(KVDP_EINVAL, "host_path must be 0 or 1");
+    if (value < 0 || value > 2) return fail(KVDP_EINVAL, "host_path must be 0, 1 or 2");
     o.host_path = value;
+  } else if (!strcmp(name, "l2_hint")) {
+    if (value < 0 || value > 3) return fail(KVDP_EINVAL, "l2_hint must be 0..3");
+    o.l2_hint = value;
   } else if (!strcmp(name, "host_ctas")) {
     if (value < 0 || value > 4096) return fail(KVDP_EINVAL, "host_ctas out of range");
     o.host_ctas = value;
@@ -107,6 +110,7 @@ int64_t kvdp_get_option(const char* name) {
   if (!strcmp(name, "ctas_per_sm")) return o.ctas_per_sm;
   if (!strcmp(name, "host_path")) return o.host_path;
   if (!strcmp(name, "host_ctas")) return o.host_ctas;
+  if (!strcmp(name, "l2_hint")) return o.l2_hint;
   return -1;
 }
 

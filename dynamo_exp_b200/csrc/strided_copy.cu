@@ -243,6 +243,7 @@ __global__ void __launch_bounds__(32) kvdp_copy_tma_tma_kernel(const __grid_cons
     const int64_t first = blockIdx.x;
     const int64_t step = gridDim.x;
     const int64_t n = first < a.total_tiles ? (a.total_tiles - first + step - 1) / step : 0;
+    const uint64_t pol = a.l2_hint ? l2_policy_evict_first() : 0;
     for (int64_t it = 0; it < n + kTmaLoadsAhead; ++it) {
       const int64_t j = it - kTmaLoadsAhead;  // tile whose store is issued now
       if (j >= 0 && j < n) {
@@ -250,7 +251,11 @@ __global__ void __launch_bounds__(32) kvdp_copy_tma_tma_kernel(const __grid_cons
         const uint32_t s = (uint32_t)(j % kTmaStages);
         mbar_wait(bars + 8 * s, (uint32_t)((j / kTmaStages) & 1));
         fence_proxy_async_smem();
-        bulk_s2g((char*)(dst_base(a, t.layer, 0) + t.dst_chunk_rel + t.off), ring + s * a.tile_bytes, t.bytes);
+        char* dptr = (char*)(dst_base(a, t.layer, 0) + t.dst_chunk_rel + t.off);
+        if (a.l2_hint & 2)
+          bulk_s2g_hint(dptr, ring + s * a.tile_bytes, t.bytes, pol);
+        else
+          bulk_s2g(dptr, ring + s * a.tile_bytes, t.bytes);
         bulk_commit();
       }
       if (it < n) {
@@ -259,7 +264,10 @@ __global__ void __launch_bounds__(32) kvdp_copy_tma_tma_kernel(const __grid_cons
         // the store that last read this stage (tile it-8) must have drained its shared-memory reads
         if (it >= kTmaStages) bulk_wait_read_dyn(kTmaStages - kTmaLoadsAhead);
         mbar_expect_tx(bars + 8 * s, t.bytes);
-        bulk_g2s(ring + s * a.tile_bytes, t.src, t.bytes, bars + 8 * s);
+        if (a.l2_hint & 1)
+          bulk_g2s_hint(ring + s * a.tile_bytes, t.src, t.bytes, bars + 8 * s, pol);
+        else
+          bulk_g2s(ring + s * a.tile_bytes, t.src, t.bytes, bars + 8 * s);
       }
     }
     bulk_wait_all<0>();  // all global writes of this CTA are complete
@@ -328,7 +336,9 @@ int launch_strided_copy(CopyArgs a, uint32_t align, const CopyLaunchHints& hints
   const bool contig =
       a.row_groups == 1 && a.dst_col_offset == 0 && (a.rows == 1 || a.dst_row_stride == (int64_t)a.run_bytes);
   int path = (int)opt.copy_path;
-  if (align < 16 || hints.host_memory || a.src_row_stride != 0) path = 1;
+  const bool host_tma = hints.host_memory && opt.host_path == 2;
+  if (align < 16 || (hints.host_memory && !host_tma) || a.src_row_stride != 0) path = 1;
+  a.l2_hint = (uint32_t)opt.l2_hint;
   if (path == 0) path = contig ? 3 : 2;
   if (path == 3 && !contig) path = 2;
 
@@ -386,6 +396,7 @@ int launch_strided_copy(CopyArgs a, uint32_t align, const CopyLaunchHints& hints
       return fail(KVDP_EINVAL, "tile_bytes=%u needs %zu B shared memory (> %d)", tile, smem, di.max_smem_optin);
     if (ctas_per_sm <= 0) ctas_per_sm = std::max(1, std::min(8, (int)((size_t)di.max_smem_optin / (smem + 1024))));
     grid64 = std::min<int64_t>((int64_t)di.sm_count * ctas_per_sm, a.total_tiles);
+    if (hints.host_memory) grid64 = std::min<int64_t>(grid64, opt.host_ctas > 0 ? opt.host_ctas : 32);
     const int grid = (int)std::max<int64_t>(grid64, 1);
     if (int rc = set_smem(kvdp_copy_tma_tma_kernel, smem)) return rc;
     kvdp_copy_tma_tma_kernel<<<grid, 32, smem, stream>>>(a);

@@ -28,6 +28,7 @@ struct CopyArgs {
   // chunk's row r starts at chunk_base + r*src_row_stride + src_col_offset instead of r*row_groups*run_bytes
   int64_t src_row_stride, src_col_offset;
   uint32_t tile_bytes;
+  uint32_t l2_hint;  // path 3: bit 0 = evict_first on loads, bit 1 = on stores
   uint32_t tiles_per_chunk;
   int64_t total_tiles;
   // optional completion signal (last CTA to finish publishes *done_flag = done_value at system scope)
