@@ -349,6 +349,11 @@ class TensorView:
     def address(self, indices: Sequence[int]) -> int:
         return self.storage.get_pointer() + self.byte_offset(indices)
 
+    def indices_iter(self):
+        """All index tuples in row-major order (reference: kv/storage.rs:809-815)."""
+        for flat in range(self._total):
+            yield unflatten_index(flat, self._shape)
+
     def is_contiguous(self) -> bool:
         expected, expected_b = 1, self._element_size
         for i in range(len(self._shape) - 1, -1, -1):

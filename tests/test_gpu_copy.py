@@ -461,3 +461,48 @@ def test_full_size_round_trip_llama8b_isl4k(gpu):
         s = src[l].reshape(2, nb, chunk)
         g = got[l].reshape(2, nb, chunk)
         assert np.array_equal(g[:, did], s[:, sid]), l
+
+
+@pytest.mark.parametrize("src_kind,dst_kind", [("pinned", "pinned"), ("pinned", "device"), ("device", "pinned")])
+def test_v2_plan_with_pinned_endpoints(gpu, oracle, src_kind, dst_kind):
+    """directions H->D, D->H and P->P (v2 only: the reference rejects pinned-to-pinned, kv/layer.rs:385-387).
+    Pinned memory is reached by the SMs directly (zero-copy), all layers in one launch."""
+    L, ns, nd = 3, 7, 6
+    bd = details(KvLayout.KvFirst, L=L, H=2, D=32, bs=8)
+    kind = {"pinned": StorageType.Pinned, "device": StorageType.Device(0)}
+    a = KvBlockStorage.allocate(ns, bd, kind[src_kind])
+    b = KvBlockStorage.allocate(nd, bd, kind[dst_kind])
+    src = fill_layers(gpu, a, 21)
+    sid, did = [6, 0, 3, 3], [1, 5, 0, 2]
+    eng = TransferEngine(8)
+    eng.run(CopyPlan.block_copy(a, b), sid, did, num_layers=L)
+    eng.sync()
+    want = [np.zeros(b.layer(l).storage_size(), dtype=np.uint8) for l in range(L)]
+    oracle.copy_blocks_layers(src, want, sid, did, 2, ns, nd, bd.suffix_dim(), 2)
+    for l in range(L):
+        got = b.layer(l).storage.storage.as_numpy() if dst_kind == "pinned" else read_layers(gpu, b)[l]
+        assert np.array_equal(got, want[l]), l
+
+
+def test_v2_plan_rejects_pageable_host_memory(gpu):
+    buf = np.zeros(4096, dtype=np.uint8)
+    d = DevBuf(gpu, 4096)
+    with pytest.raises(gpu.KvdpError, match="pageable"):
+        CopyPlan.block_copy_raw([buf.ctypes.data], [d.ptr], 1, 4, 4, 1024, 1)
+
+
+def test_legacy_memcpy_falls_back_to_dma_for_pageable_memory(gpu, oracle):
+    """copy_blocks_memcpy_3d accepts any memory cudaMemcpyDefault accepts (block_copy.cu:246-305); pageable host
+    buffers cannot be read by a kernel, so that case keeps the reference's per-chunk DMA."""
+    prefix, ns, nd, suffix, elem = 2, 5, 5, 64, 2
+    n = prefix * ns * suffix * elem
+    src_h = payload(n, 77)
+    dst = DevBuf(gpu, prefix * nd * suffix * elem)
+    sid = np.array([4, 0, 2], dtype=np.int32)
+    did = np.array([1, 3, 0], dtype=np.int32)
+    rc = gpu.lib().copy_blocks_memcpy_3d(src_h.ctypes.data, dst.ptr, sid.ctypes.data, did.ctypes.data, 3, prefix, suffix,
+                                         elem, ns, nd, None)
+    assert rc == 0
+    want = np.zeros(prefix * nd * suffix * elem, dtype=np.uint8)
+    oracle.copy_blocks_3d(src_h, want, sid, did, prefix, ns, nd, suffix, elem)
+    assert np.array_equal(dst.download(), want)

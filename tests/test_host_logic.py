@@ -120,3 +120,51 @@ def test_block_map_validation():
     with pytest.raises(KvError, match="same length"):
         CopyStreamBlockMap([1, 2], [2], 1, 1, 1, 1, 2).validate()
     CopyStreamBlockMap([1], [2], 2, 4, 4, 8, 2).validate()
+
+
+# ---- the reference's own TensorView unit tests, value for value (kv/storage.rs:1260-1516) ----
+def test_ref_tensor_view_creation_and_indexing():
+    v = TensorView(MockTensor(96), [2, 3, 4], 4)                      # :1260-1279
+    assert v.shape() == [2, 3, 4] and v.strides() == [12, 4, 1] and v.byte_strides() == [48, 16, 4]
+    assert v.num_elements() == 24 and v.size_in_bytes() == 96 and v.is_contiguous()
+    for idx, flat in (([0, 0, 0], 0), ([0, 0, 1], 1), ([0, 1, 0], 4), ([1, 0, 0], 12), ([1, 2, 3], 23)):   # :1295-1299
+        assert v.flat_index(idx) == flat
+    for idx, off in (([0, 0, 0], 0), ([0, 0, 1], 4), ([0, 1, 0], 16), ([1, 0, 0], 48)):                    # :1302-1305
+        assert v.byte_offset(idx) == off
+    assert v.address([0, 0, 0]) == 0x1000 and v.address([0, 0, 1]) == 0x1004                               # :1308-1310
+    assert v.address([1, 2, 3]) == 0x1000 + 23 * 4
+
+
+def test_ref_tensor_view_slicing():
+    v = TensorView(MockTensor(96), [2, 3, 4], 4)                      # :1313-1343
+    s = v.slice(1, 1, 3)
+    assert s.shape() == [2, 2, 4] and s.strides() == [12, 4, 1] and s.byte_strides() == [48, 16, 4] and s.offset == 16
+    assert s.address([0, 0, 0]) == 0x1000 + 16
+    assert s.address([1, 1, 3]) == 0x1000 + 16 + 48 + 16 + 12
+
+
+def test_ref_custom_strides_and_offsets():
+    t = MockTensor(96)                                                # :1345-1406
+    nc = TensorView.with_strides(t, [2, 2, 4], [12, 4, 1], 0, 4)
+    assert not nc.is_contiguous() and nc.strides() == [12, 4, 1] and nc.byte_strides() == [48, 16, 4]
+    assert nc.byte_offset([1, 1, 3]) == (12 + 4 + 3) * 4 < t.storage_size()
+    with pytest.raises(KvError, match="would access up to byte offset 108"):
+        TensorView.with_strides(t, [2, 3, 4], [16, 4, 1], 0, 4)
+    t2 = MockTensor(120)                                              # :1408-1454
+    ov = TensorView.with_strides(t2, [2, 3, 4], [12, 4, 1], 16, 4)
+    assert ov.is_contiguous() and ov.offset == 16
+    assert ov.byte_offset([0, 0, 0]) == 16 and ov.byte_offset([1, 2, 3]) == 16 + (12 + 2 * 4 + 3) * 4
+    with pytest.raises(KvError, match="would access up to byte offset"):
+        TensorView.with_strides(t2, [2, 3, 4], [12, 4, 1], 80, 4)
+
+
+def test_ref_in_bounds_validate_and_indices_iter():
+    v = TensorView(MockTensor(96), [2, 3, 4], 4)                      # :1456-1493
+    assert v.in_bounds([0, 0, 0]) and v.in_bounds([1, 2, 3])
+    for bad in ([2, 0, 0], [0, 3, 0], [0, 0, 4], [2, 3, 4]):
+        assert not v.in_bounds(bad)
+    for bad in ([2, 0, 0], [0, 3, 0], [0, 0, 4]):
+        with pytest.raises(KvError):
+            v.byte_offset(bad)
+    v2 = TensorView(MockTensor(24), [2, 3], 4)                        # :1495-1514
+    assert list(v2.indices_iter()) == [[0, 0], [0, 1], [0, 2], [1, 0], [1, 1], [1, 2]]
