@@ -199,7 +199,7 @@ def host_tier_bench(torch, lib):
     """BASELINE config 4: offload / onboard of Llama-3-8B blocks between HBM (layer-separate) and a pinned
     contiguous-per-block host slab, mixed ISL 1k..32k (16..512 blocks per request), through kvdp_host_tier_*."""
     L = lib.lib()
-    isl_blocks = [16, 32, 64, 128, 256, 16]           # 1k, 2k, 4k, 8k, 16k (+1k) = 512 blocks = 4 GiB
+    isl_blocks = [16, 32, 64, 128, 256, 512]          # ISL 1k, 2k, 4k, 8k, 16k, 32k = 1008 blocks = 7.9 GiB
     nb = sum(isl_blocks)
     dev_layers = [torch.empty(2 * nb * CHUNK, dtype=torch.uint8, device="cuda").random_(0, 256) for _ in range(L8B)]
     back_layers = [torch.zeros(2 * nb * CHUNK, dtype=torch.uint8, device="cuda") for _ in range(L8B)]
@@ -255,7 +255,8 @@ def host_tier_bench(torch, lib):
     L.kvdp_host_tier_destroy(tier_b)
     L.cuda_free_host(host)
     payload = nb * BLOCK_BYTES
-    return {"workload": "Llama-3-8B blocks, requests of %s blocks (ISL 1k..16k mix), 4 GiB per direction" % isl_blocks,
+    return {"workload": "Llama-3-8B blocks, requests of %s blocks (ISL 1k..32k mix), %.1f GiB per direction"
+                        % (isl_blocks, nb * BLOCK_BYTES / 2 ** 30),
             "offload_GBps": payload / t_off / GB, "onboard_GBps": payload / t_on / GB,
             "d2h_link_ceiling_GBps": ceil["d2h"], "h2d_link_ceiling_GBps": ceil["h2d"],
             "offload_frac_of_ceiling": payload / t_off / GB / ceil["d2h"],
@@ -381,6 +382,25 @@ def hash_bench(torch, lib, steps, warmup, peak):
     b.record(streams[0])
     torch.cuda.synchronize()
     sec_serial = a.elapsed_time(b) / 1e3 / steps
+    # spot parity inside the timed configuration, against an implementation that is neither ours nor the oracle
+    try:
+        import xxhash
+        run(1337, 0)
+        torch.cuda.synchronize()
+        t_host = tok[:4 * BS].cpu().numpy().astype(np.uint32)
+        got_bh = outs[0][1][:4].cpu().numpy().view(np.uint64)
+        got_sh = outs[0][2][:4].cpu().numpy().view(np.uint64)
+        parent = None
+        for bi in range(4):
+            want = xxhash.xxh3_64_intdigest(t_host[bi * BS:(bi + 1) * BS].tobytes(), seed=1337)
+            seq = want if parent is None else xxhash.xxh3_64_intdigest(
+                int(parent).to_bytes(8, "little") + int(want).to_bytes(8, "little"), seed=1337)
+            if int(got_bh[bi]) != want or int(got_sh[bi]) != seq:
+                raise RuntimeError("hash bench: GPU hashes differ from xxhash")
+            parent = seq
+        spot = "first 4 blocks of request 0 equal python-xxhash (block and chained)"
+    except ImportError:
+        spot = "python xxhash not importable: no in-bench spot check"
     # (2) throughput with batches alternating over the two streams
     start = torch.cuda.Event(enable_timing=True)
     ends = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
@@ -409,7 +429,8 @@ def hash_bench(torch, lib, steps, warmup, peak):
     torch.cuda.synchronize()
     sec_un = a.elapsed_time(b) / 1e3 / steps
     out = {"hashes_per_s": nblk / sec_serial, "tokens_per_s": total / sec_serial, "ms_per_batch": sec_serial * 1e3,
-           "requests": n_req, "blocks": nblk, "launches_per_batch": 5,
+           "requests": n_req, "blocks": nblk, "launches_per_batch": 5, "batches_timed": steps,
+           "requests_timed": n_req * steps, "spot_check": spot,
            "semantics": "lib/tokens: block_hash + chained sequence_hash per full 64-token block, one stream",
            "two_stream_pipeline": {"hashes_per_s": nblk / sec, "ms_per_batch": sec * 1e3},
            "unchained_router_form": {"hashes_per_s": nblk / sec_un, "ms_per_batch": sec_un * 1e3,
@@ -486,7 +507,7 @@ def run_single(args):
         line["host_tier"] = host_tier_bench(torch, lib)
         torch.cuda.empty_cache()
     if not args.no_hash:
-        line["hash"] = hash_bench(torch, lib, 10, 3, peak)
+        line["hash"] = hash_bench(torch, lib, 18, 3, peak)   # 18 x 57 344 = 1.03 M requests per timed loop
         line["hashes_per_s"] = line["hash"]["hashes_per_s"]
         line["router_index"] = router_index_bench(torch, lib)
     if not args.no_cpu:
