@@ -74,3 +74,23 @@ def test_oracle_is_not_linked_or_imported_by_the_product():
                 assert "kvoracle" not in text and "oracle/" not in text and "import oracle" not in text, f
     ldd = subprocess.run(["ldd", os.path.join(pkg, "libkvdp.so")], capture_output=True, text=True).stdout
     assert "kvoracle" not in ldd
+
+
+def test_rust_sys_crate_declares_every_header_function():
+    """rust/kvdp-sys is shipped as source only (no Rust toolchain here); at least keep it in step with the header."""
+    text = open(os.path.join(ROOT, "rust", "kvdp-sys", "src", "lib.rs")).read()
+    declared = sorted(set(re.findall(r"pub fn ([a-z_0-9]+)\(", text)))
+    assert declared == header_functions()
+    # struct layout mirror: every kvdp_plan_desc field appears, in header order
+    hdr = open(HEADER).read()
+    body = hdr[hdr.index("typedef struct kvdp_plan_desc {"):hdr.index("} kvdp_plan_desc;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    fields = []
+    for stmt in body.split("{", 1)[1].split(";"):
+        stmt = stmt.strip()
+        if not stmt:
+            continue
+        names = re.sub(r"^(const\s+)?[a-z0-9_]+\s*\*?", "", stmt)
+        fields += [n.strip().lstrip("*").strip() for n in names.split(",")]
+    rust = re.findall(r"pub ([a-z_]+): ", text[text.index("pub struct KvdpPlanDesc"):text.index("pub const KVDP_OK")])
+    assert rust == fields
