@@ -265,6 +265,45 @@ def host_tier_bench(torch, lib):
             "staging": "2 x 32 blocks (2 x 256 MiB HBM), one DMA per request range, gather/scatter kernel per slot"}
 
 
+def event_publish_bench(lib, n_events=20000, blocks_per_event=4, bs=64):
+    """the engine-facing event ABI. One engine thread publishes stored events (4 full 64-token blocks
+    each, chained parents) as fast as it can; the publisher thread hashes whatever queued up per GPU batch and applies
+    the events to a prefix index. Wall clock from the first publish to the flush returning (host path: no device
+    timer applies)."""
+    L = lib.lib()
+    rng = np.random.Generator(np.random.PCG64(7))
+    toks = rng.integers(0, 128256, size=(n_events, blocks_per_event * bs), dtype=np.uint32)
+    ix = C.c_void_p()
+    lib.check(L.kvdp_index_create(C.byref(ix), 1 << 18, 64, 0))
+    if L.dynamo_llm_init(b"bench", b"worker", 1, bs) != 0:
+        raise RuntimeError("dynamo_llm_init failed")
+    lib.check(L.kvdp_event_sink_index(ix, 0))
+    counts = (C.c_size_t * blocks_per_event)(*([bs] * blocks_per_event))
+    ids = (C.c_uint64 * blocks_per_event)()
+    u32p = C.POINTER(C.c_uint32)
+    b0 = [int(L.kvdp_event_stat(i)) for i in range(4)]
+    t0 = time.perf_counter()
+    for e in range(n_events):
+        for j in range(blocks_per_event):
+            ids[j] = e * blocks_per_event + j + 1
+        if L.dynamo_kv_event_publish_stored(e, toks[e].ctypes.data_as(u32p), counts, ids, blocks_per_event, None, 0):
+            raise RuntimeError("publish failed")
+    t_pub = time.perf_counter() - t0
+    lib.check(L.kvdp_event_flush())
+    t_all = time.perf_counter() - t0
+    b1 = [int(L.kvdp_event_stat(i)) for i in range(4)]
+    nodes = int(L.kvdp_index_stat(ix, 0, 0))
+    lib.check(L.kvdp_event_sink_index(None, 0))
+    L.dynamo_llm_shutdown()
+    L.kvdp_index_destroy(ix)
+    assert b1[1] - b0[1] == n_events and nodes >= n_events
+    return {"events_per_s": n_events / t_all, "blocks_per_s": n_events * blocks_per_event / t_all,
+            "publish_call_us": t_pub / n_events * 1e6, "events": n_events, "blocks_per_event": blocks_per_event,
+            "hash_batches": b1[2] - b0[2], "avg_blocks_per_batch": (b1[3] - b0[3]) / max(1, b1[2] - b0[2]),
+            "note": "dynamo_kv_event_publish_stored from one Python thread (ctypes call overhead included); sink = "
+                    "prefix index; batches form by themselves while the previous one is on the GPU"}
+
+
 def router_index_bench(torch, lib, steps=10):
     """the router's prefix index. 8 workers hold prefixes of 256 synthetic documents; 57 344 requests
     (ISL 512..32k -> 8..512 block hashes each) share a document prefix of random length and then diverge. One launch
@@ -510,6 +549,7 @@ def run_single(args):
         line["hash"] = hash_bench(torch, lib, 18, 3, peak)   # 18 x 57 344 = 1.03 M requests per timed loop
         line["hashes_per_s"] = line["hash"]["hashes_per_s"]
         line["router_index"] = router_index_bench(torch, lib)
+        line["event_publish"] = event_publish_bench(lib)
     if not args.no_cpu:
         from oracle import kvoracle as ko
         threads = ko.hw_threads()

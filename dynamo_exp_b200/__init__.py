@@ -10,6 +10,7 @@ from .layer import (CopyStream, CopyStreamBlockMap, KvBlockDetails, KvBlockStora
                     KvModelDetails)
 from .tokens import (PartialTokenBlock, TokenBlock, TokenBlockSequence, Tokens, TwinTokens, XXH3_SEED,  # noqa: F401
                      compute_block_hash_for_seq, compute_hash, hash_token_blocks)
+from .publisher import KvEventPublisher  # noqa: F401
 from .transfer import CopyPlan, HostTier, KvContiguousBlocks, TransferEngine  # noqa: F401
 
 __version__ = "0.2.0"

@@ -125,6 +125,19 @@ PROTOTYPES = {
     "kvdp_index_flush": (_i, [_vp]),
     "kvdp_index_find_matches": (_i, [_vp, _vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp]),
     "kvdp_index_stat": (_i64, [_vp, _i32, _u64]),
+    # §I engine-facing KV-event ABI (argtypes as in the reference's CtypesEventPublisher fixture,
+    # lib/bindings/python/tests/test_kv_bindings.py:141-176)
+    "dynamo_llm_init": (C.c_uint32, [C.c_char_p, C.c_char_p, _i64, C.c_uint32]),
+    "dynamo_llm_shutdown": (C.c_uint32, []),
+    "dynamo_llm_load_publisher_create": (C.c_uint32, []),
+    "dynamo_kv_event_publish_stored": (C.c_uint32, [_u64, C.POINTER(C.c_uint32), C.POINTER(C.c_size_t),
+                                                    C.POINTER(_u64), C.c_size_t, C.POINTER(_u64), _u64]),
+    "dynamo_kv_event_publish_removed": (C.c_uint32, [_u64, C.POINTER(_u64), C.c_size_t]),
+    "kvdp_event_sink_callback": (_i, [_vp, _vp]),
+    "kvdp_event_sink_index": (_i, [_vp, _i32]),
+    "kvdp_event_flush": (_i, []),
+    "kvdp_event_poll": (_i, [_vp, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "kvdp_event_stat": (_i64, [_i32]),
 }
 
 _lib = None

@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libkvdp.so")
 STAMP = os.path.join(HERE, ".libkvdp.stamp")
 
-SOURCES = ["runtime.cu", "strided_copy.cu", "plan_xfer.cu", "legacy_abi.cu", "token_hash.cu", "hash_static.cu", "host_tier.cu", "prefix_index.cu"]
+SOURCES = ["runtime.cu", "strided_copy.cu", "plan_xfer.cu", "legacy_abi.cu", "token_hash.cu", "hash_static.cu", "host_tier.cu", "prefix_index.cu", "event_capi.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -20,6 +20,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <unordered_map>
 #include <vector>
 
@@ -142,6 +143,7 @@ struct kvdp_index {
   size_t stage_cap = 0;
   cudaStream_t stream = nullptr;
   bool full_upload_needed = true;
+  std::recursive_mutex mu;  // events may arrive from the publisher thread while another thread scores requests
 };
 
 namespace {
@@ -279,6 +281,7 @@ kvdp_stream_t kvdp_index_stream(kvdp_index* ix) { return ix ? (kvdp_stream_t)ix-
 int kvdp_index_apply_stored(kvdp_index* ix, int32_t worker, int32_t has_parent, uint64_t parent_hash,
                             const uint64_t* block_hashes, const uint64_t* tokens_hashes, int32_t n) {
   if (!ix) return fail(KVDP_EINVAL, "kvdp_index_apply_stored: NULL handle");
+  std::lock_guard<std::recursive_mutex> guard(ix->mu);
   if (worker < 0 || worker >= ix->max_workers) return fail(KVDP_EINVAL, "prefix index: worker slot %d out of range", worker);
   if (n < 0 || (n > 0 && (!block_hashes || !tokens_hashes))) return fail(KVDP_EINVAL, "prefix index: bad block arrays");
   ix->lookup_present[worker] = true;
@@ -321,6 +324,7 @@ int kvdp_index_apply_stored(kvdp_index* ix, int32_t worker, int32_t has_parent, 
 // indexer.rs:344-376
 int kvdp_index_apply_removed(kvdp_index* ix, int32_t worker, const uint64_t* block_hashes, int32_t n) {
   if (!ix) return fail(KVDP_EINVAL, "kvdp_index_apply_removed: NULL handle");
+  std::lock_guard<std::recursive_mutex> guard(ix->mu);
   if (worker < 0 || worker >= ix->max_workers) return fail(KVDP_EINVAL, "prefix index: worker slot %d out of range", worker);
   if (n < 0 || (n > 0 && !block_hashes)) return fail(KVDP_EINVAL, "prefix index: bad block array");
   ix->lookup_present[worker] = true;
@@ -343,6 +347,7 @@ int kvdp_index_apply_removed(kvdp_index* ix, int32_t worker, const uint64_t* blo
 // indexer.rs:380-386
 int kvdp_index_remove_worker(kvdp_index* ix, int32_t worker) {
   if (!ix) return fail(KVDP_EINVAL, "kvdp_index_remove_worker: NULL handle");
+  std::lock_guard<std::recursive_mutex> guard(ix->mu);
   if (worker < 0 || worker >= ix->max_workers) return fail(KVDP_EINVAL, "prefix index: worker slot %d out of range", worker);
   if (!ix->lookup_present[worker]) return 0;
   for (auto& kv : ix->lookup[worker]) {
@@ -360,6 +365,7 @@ int kvdp_index_remove_worker(kvdp_index* ix, int32_t worker) {
 // Push every pending change to the device (asynchronous on the index's stream).
 int kvdp_index_flush(kvdp_index* ix) {
   if (!ix) return fail(KVDP_EINVAL, "kvdp_index_flush: NULL handle");
+  std::lock_guard<std::recursive_mutex> guard(ix->mu);
   DeviceGuard g(ix->device);
   if (ix->full_upload_needed) {
     KVDP_CUDA(cudaMemcpyAsync(ix->d_edges, ix->h_edges.data(), sizeof(EdgeRec) * ix->capacity, cudaMemcpyHostToDevice,
@@ -392,6 +398,7 @@ int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int6
                             int32_t early_exit, int32_t num_workers, uint32_t* d_scores, int32_t* d_matched_depth,
                             kvdp_stream_t stream_) {
   if (!ix) return fail(KVDP_EINVAL, "kvdp_index_find_matches: NULL handle");
+  std::lock_guard<std::recursive_mutex> guard(ix->mu);
   if (n_req < 0) return fail(KVDP_EINVAL, "prefix index: negative n_req");
   if (num_workers < 1 || num_workers > ix->max_workers) return fail(KVDP_EINVAL, "prefix index: num_workers out of range");
   if (n_req == 0) return 0;
@@ -412,6 +419,7 @@ int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int6
 //        5: workers that ever had a lookup table and still do
 int64_t kvdp_index_stat(kvdp_index* ix, int32_t what, uint64_t arg) {
   if (!ix) return -1;
+  std::lock_guard<std::recursive_mutex> guard(ix->mu);
   switch (what) {
     case 0: return (int64_t)ix->nodes.size();
     case 1: return arg < ix->nodes.size() ? (int64_t)ix->nodes[arg].children.size() : -1;

@@ -291,6 +291,44 @@ int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int6
  * `arg`; 4 root's child for tokens hash `arg` (node id or -1); 5 workers with a lookup table. */
 int64_t kvdp_index_stat(kvdp_index* ix, int32_t what, uint64_t arg);
 
+/* ================================================================== §I. Engine-facing KV-event ABI
+ * The five symbols of the reference's libdynamo_llm_capi.so (lib/bindings/c/src/lib.rs:50-311), which the patched vLLM
+ * loads from $VLLM_KV_CAPI_PATH with ctypes: same names, argument meaning and 0/1 results, so pointing that variable at
+ * libkvdp.so swaps the implementation. Token blocks are hashed with seed 1337 exactly as compute_block_hash_for_seq
+ * does (kv_router/indexer.rs:123-135), but in batches on the GPU: the calls only queue; one publisher thread hashes
+ * everything that queued up in one launch and emits the events in arrival order. The reference's transport (NATS,
+ * subject "namespace.<ns>.component.<component>.kv_events", payload = RouterEvent JSON) is not rebuilt: the sink is
+ * chosen with kvdp_event_sink_* below. Differences from the reference, on purpose: publishing before dynamo_llm_init
+ * returns ERR (the reference aborts the process); after dynamo_llm_shutdown a new dynamo_llm_init is accepted. */
+typedef uint32_t dynamo_llm_result_t;
+#define DYNAMO_LLM_OK 0u
+#define DYNAMO_LLM_ERR 1u
+dynamo_llm_result_t dynamo_llm_init(const char* namespace_c_str, const char* component_c_str, int64_t worker_id,
+                                    uint32_t kv_block_size);                                  /* lib.rs:50-113 */
+dynamo_llm_result_t dynamo_llm_shutdown(void);                                                /* lib.rs:115-128 */
+dynamo_llm_result_t dynamo_llm_load_publisher_create(void);                                   /* lib.rs:130-133 */
+/* parent_hash == NULL means "no parent". Blocks whose token count differs from kv_block_size end the list (:191-210). */
+dynamo_llm_result_t dynamo_kv_event_publish_stored(uint64_t event_id, const uint32_t* token_ids,
+                                                   const size_t* num_block_tokens, const uint64_t* block_ids,
+                                                   size_t num_blocks, const uint64_t* parent_hash,
+                                                   uint64_t lora_id);                         /* lib.rs:260-295 */
+dynamo_llm_result_t dynamo_kv_event_publish_removed(uint64_t event_id, const uint64_t* block_ids,
+                                                    size_t num_blocks);                       /* lib.rs:297-311 */
+/* Sinks (no reference counterpart). A callback receives every event as (subject, RouterEvent JSON, length) on the
+ * publisher thread; an index sink applies the events to a prefix index under worker slot `worker_slot` (either, both or
+ * neither may be set; pass NULL to clear). With neither, events wait in an outbox of 65 536 entries for
+ * kvdp_event_poll: returns 1 and copies one event (not NUL-terminated, *len bytes), 0 when empty, KVDP_ERANGE with
+ * *len = bytes needed when `cap` is too small. kvdp_event_flush blocks until every event published so far has been
+ * hashed and delivered. kvdp_event_stat: 0 submitted, 1 delivered, 2 hash batches, 3 blocks hashed, 4 short blocks
+ * that ended a list, 5 stored events skipped by the index (unknown parent), 6 events lost to a failed hash batch,
+ * 7 outbox overflow drops, 8 outbox length. */
+typedef void (*kvdp_event_cb)(void* user, const char* subject, const char* json, size_t len);
+int kvdp_event_sink_callback(kvdp_event_cb cb, void* user);
+int kvdp_event_sink_index(kvdp_index* ix, int32_t worker_slot);
+int kvdp_event_flush(void);
+int kvdp_event_poll(char* buf, size_t cap, size_t* len);
+int64_t kvdp_event_stat(int32_t what);
+
 #ifdef __cplusplus
 }
 #endif

@@ -110,4 +110,15 @@ extern "C" {
     pub fn kvdp_index_flush(ix: *mut KvdpIndex) -> c_int;
     pub fn kvdp_index_find_matches(ix: *mut KvdpIndex, d_hashes: *const u64, d_seq_offsets: *const i64, n_req: i64, early_exit: i32, num_workers: i32, d_scores: *mut u32, d_matched_depth: *mut i32, stream: *mut c_void) -> c_int;
     pub fn kvdp_index_stat(ix: *mut KvdpIndex, what: i32, arg: u64) -> i64;
+    // §I engine-facing KV-event ABI (same symbols as libdynamo_llm_capi.so)
+    pub fn dynamo_llm_init(namespace_c_str: *const c_char, component_c_str: *const c_char, worker_id: i64, kv_block_size: u32) -> u32;
+    pub fn dynamo_llm_shutdown() -> u32;
+    pub fn dynamo_llm_load_publisher_create() -> u32;
+    pub fn dynamo_kv_event_publish_stored(event_id: u64, token_ids: *const u32, num_block_tokens: *const usize, block_ids: *const u64, num_blocks: usize, parent_hash: *const u64, lora_id: u64) -> u32;
+    pub fn dynamo_kv_event_publish_removed(event_id: u64, block_ids: *const u64, num_blocks: usize) -> u32;
+    pub fn kvdp_event_sink_callback(cb: Option<unsafe extern "C" fn(user: *mut c_void, subject: *const c_char, json: *const c_char, len: usize)>, user: *mut c_void) -> c_int;
+    pub fn kvdp_event_sink_index(ix: *mut KvdpIndex, worker_slot: i32) -> c_int;
+    pub fn kvdp_event_flush() -> c_int;
+    pub fn kvdp_event_poll(buf: *mut c_char, cap: usize, len: *mut usize) -> c_int;
+    pub fn kvdp_event_stat(what: i32) -> i64;
 }

@@ -19,7 +19,7 @@ def header_functions():
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     src = re.sub(r"^\s*#.*$", "", src, flags=re.M)
     names = re.findall(r"\b([a-z_0-9]+)\s*\([^;{}]*\)\s*;", src)
-    return sorted(set(n for n in names if n.startswith(("kvdp_", "copy_", "cuda_"))))
+    return sorted(set(n for n in names if n.startswith(("kvdp_", "copy_", "cuda_", "dynamo_"))))
 
 
 def test_header_declares_the_14_legacy_symbols():
