@@ -59,3 +59,7 @@ run([32768] * (tot // 32768), True, "all ISL 32k, chained")
 run([64] * 70000, False, "70k one-block requests (3-kernel scan)")
 run(mix * 4, False, "router mix x4, un-chained")
 run(mix * 4, True, "router mix x4, chained")
+big = mix * 4
+run(big, True, "router mix x4, chained")
+run(sorted(big), True, "router mix x4 SORTED by length, chained")
+run(sorted(big), False, "router mix x4 SORTED by length, un-chained")
