@@ -267,17 +267,16 @@ __global__ void __launch_bounds__(WARPS * 32) kvdp_hash_blocks_tma(const __grid_
 
   const int64_t total = __ldg(A.block_offsets + A.n_req);
   const int64_t tiles = (total + 31) >> 5;
-  uint32_t parity = 0;
   // Each warp owns a CONTIGUOUS range of tiles: one binary search for its first block, then the request index only
   // walks forward (a per-tile binary search over 10^4..10^6 requests cost ~40% of the kernel's time).
   const int64_t warps_total = (int64_t)gridDim.x * WARPS;
   const int64_t tiles_per_warp = (tiles + warps_total - 1) / warps_total;
-  const int64_t t_begin = ((int64_t)blockIdx.x * WARPS + warp) * tiles_per_warp;
+  const int64_t t_begin = min(tiles, ((int64_t)blockIdx.x * WARPS + warp) * tiles_per_warp);
   const int64_t t_end = min(tiles, t_begin + tiles_per_warp);
-  int64_t r_tile = -1;  // request holding the first block of the current tile (warp-uniform)
-  for (int64_t t = t_begin; t < t_end; ++t) {
+  int64_t r_tile = -1;  // request holding the first block of the tile being issued (warp-uniform)
+  // Start the copies of tile t: every lane arrives once on the warp's barrier, through its copy's byte count or directly.
+  auto issue = [&](int64_t t) {
     const int64_t gb = t * 32 + lane;
-    const bool valid = gb < total;
     if (r_tile < 0) {
       int64_t lo = 0, hi = A.n_req;  // invariant: block_offsets[lo] <= t*32 < block_offsets[hi]
       while (hi - lo > 1) {
@@ -290,7 +289,7 @@ __global__ void __launch_bounds__(WARPS * 32) kvdp_hash_blocks_tma(const __grid_
       r_tile = lo;
     }
     while (r_tile + 1 < A.n_req && __ldg(A.block_offsets + r_tile + 1) <= t * 32) ++r_tile;
-    if (valid) {
+    if (gb < total) {
       int64_t r = r_tile;
       while (r + 1 < A.n_req && __ldg(A.block_offsets + r + 1) <= gb) ++r;
       const uint32_t* src =
@@ -307,8 +306,15 @@ __global__ void __launch_bounds__(WARPS * 32) kvdp_hash_blocks_tma(const __grid_
     } else {
       mbar_arrive(bar);
     }
+  };
+  uint32_t parity = 0;
+  if (t_begin < t_end) issue(t_begin);
+  for (int64_t t = t_begin; t < t_end; ++t) {
+    const int64_t gb = t * 32 + lane;
+    const bool valid = gb < total;
     mbar_wait(bar, parity);
     parity ^= 1;
+    uint64_t hash = 0;
     if (valid) {
       uint64_t acc[8] = {P32_3, P64_1, P64_2, P64_3, P64_4, P32_2, P64_5, P32_1};
 #pragma unroll
@@ -327,9 +333,11 @@ __global__ void __launch_bounds__(WARPS * 32) kvdp_hash_blocks_tma(const __grid_
       uint64_t h = (uint64_t)LEN * P64_1;
 #pragma unroll
       for (int i = 0; i < 4; ++i) h += fold128(acc[2 * i] ^ S.fin[2 * i], acc[2 * i + 1] ^ S.fin[2 * i + 1]);
-      A.block_hash[gb] = avalanche(h);
+      hash = avalanche(h);
     }
-    __syncwarp();
+    __syncwarp();                     // every lane has read its row and has seen this phase complete
+    if (t + 1 < t_end) issue(t + 1);  // the next tile's copies fly while this tile's results are stored
+    if (valid) A.block_hash[gb] = hash;
   }
 }
 
