@@ -133,6 +133,7 @@ struct kvdp_index {
   std::vector<HostNode> nodes;
   std::unordered_map<uint64_t, uint32_t> lookup[64];
   bool lookup_present[64] = {};
+  int64_t member_nodes[64] = {};  // nodes whose worker set holds this slot (0 after remove_worker = slot reusable)
   std::vector<EdgeRec> h_edges;
   EdgeRec* d_edges = nullptr;
   std::vector<uint32_t> dirty_edges;
@@ -313,6 +314,7 @@ int kvdp_index_apply_stored(kvdp_index* ix, int32_t worker, int32_t has_parent, 
     HostNode& b = ix->nodes[block];
     if (!(b.workers >> worker & 1ULL)) {
       b.workers |= 1ULL << worker;
+      ++ix->member_nodes[worker];
       mark_node(ix, block);
     }
     lk[block_hashes[i]] = block;
@@ -333,6 +335,7 @@ int kvdp_index_apply_removed(kvdp_index* ix, int32_t worker, const uint64_t* blo
     auto it = lk.find(block_hashes[i]);
     if (it == lk.end()) continue;  // "Failed to find block to remove; skipping remove operation"
     HostNode& b = ix->nodes[it->second];
+    if (b.workers >> worker & 1ULL) --ix->member_nodes[worker];
     b.workers &= ~(1ULL << worker);
     if (b.workers == 0) {
       b.children.clear();  // no worker holds this block, so none holds its descendants through it
@@ -354,6 +357,7 @@ int kvdp_index_remove_worker(kvdp_index* ix, int32_t worker) {
     HostNode& b = ix->nodes[kv.second];
     if (b.workers >> worker & 1ULL) {
       b.workers &= ~(1ULL << worker);
+      --ix->member_nodes[worker];
       mark_node(ix, kv.second);
     }
   }
@@ -416,7 +420,7 @@ int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int6
 // sizes of the host-side structures, for the reference tests' assertions:
 // what = 0: number of nodes; 1: live edges out of `arg` (node id); 2: entries in worker `arg`'s lookup table;
 //        3: popcount of node `arg`'s worker set; 4: child of the root for tokens hash `arg` (node id or -1);
-//        5: workers that ever had a lookup table and still do
+//        5: workers that ever had a lookup table and still do; 6: nodes whose worker set holds slot `arg`
 int64_t kvdp_index_stat(kvdp_index* ix, int32_t what, uint64_t arg) {
   if (!ix) return -1;
   std::lock_guard<std::recursive_mutex> guard(ix->mu);
@@ -434,6 +438,7 @@ int64_t kvdp_index_stat(kvdp_index* ix, int32_t what, uint64_t arg) {
       for (int w = 0; w < 64; ++w) c += ix->lookup_present[w] ? 1 : 0;
       return c;
     }
+    case 6: return arg < 64 ? ix->member_nodes[arg] : -1;
     default: return -1;
   }
 }

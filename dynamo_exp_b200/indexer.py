@@ -119,7 +119,8 @@ class RadixTree:
         if s is None and create:
             free = [i for i, w in enumerate(self._worker_of_slot) if w is None]
             if not free:
-                raise KvError(f"the prefix index holds at most {MAX_WORKERS} distinct worker ids over its lifetime")
+                raise KvError(f"the prefix index holds at most {MAX_WORKERS} workers at a time (removed workers that "
+                              "left stale blocks behind keep their slot)")
             s = free[0]
             self._slot[worker_id] = s
             self._worker_of_slot[s] = worker_id
@@ -147,9 +148,12 @@ class RadixTree:
         if slot is None:
             return
         _lib.check(_lib.lib().kvdp_index_remove_worker(self._h, slot))
-        # The slot stays bound to this worker id: like the reference, a block whose lookup entry was overwritten keeps
-        # the removed worker in its set (remove_worker only visits the lookup table, indexer.rs:380-386), and such a
-        # stale membership must keep reporting under the old id, not under whoever would reuse the slot.
+        # Like the reference, a block whose lookup entry was overwritten keeps the removed worker in its set
+        # (remove_worker only visits the lookup table, indexer.rs:380-386); such a stale membership must keep reporting
+        # under the old id, so the slot stays bound to it. Only when no node holds the slot any more is it recycled.
+        if self.stat(6, slot) == 0:
+            del self._slot[worker]
+            self._worker_of_slot[slot] = None
 
     def find_matches_batch(self, sequences: Sequence[Sequence[int]], early_exit: bool = False) -> List[OverlapScores]:
         """Score many requests (each a list of LocalBlockHash) in one launch."""
@@ -258,3 +262,74 @@ class KvIndexer:
         boff, bh, _ = hash_token_blocks(flat, offs, self.kv_block_size, XXH3_SEED, chained=False)
         scores, _ = self.tree.find_matches_device_arrays(bh if bh.size else np.zeros(1, dtype=np.uint64), boff, False)
         return [self.tree._to_overlap(row) for row in scores]
+
+
+class KvIndexerSharded:
+    """reference: KvIndexerSharded (indexer.rs:677-884): several independent radix trees, every worker bound to the
+    shard that had the fewest workers when its first event arrived; a lookup asks every shard and merges the answers.
+    Here each shard is one device-resident prefix index, which also lifts the 64-worker limit of a single index to
+    64 x num_shards. Like the reference, a worker's binding is dropped by remove_worker and chosen afresh afterwards."""
+
+    def __init__(self, num_shards: int, kv_block_size: int, max_nodes: int = 1 << 20, device: int = -1):
+        if num_shards < 1:
+            raise KvError("num_shards must be at least 1")
+        self.kv_block_size = int(kv_block_size)
+        self.shards = [RadixTree(max_nodes, device) for _ in range(int(num_shards))]
+        self.worker_assignments: Dict[WorkerId, int] = {}
+        self.worker_counts = [0] * int(num_shards)
+
+    def block_size(self) -> int:
+        return self.kv_block_size
+
+    def apply_event(self, event: RouterEvent) -> None:
+        shard = self.worker_assignments.get(event.worker_id)
+        if shard is None:
+            shard = min(range(len(self.shards)), key=lambda i: self.worker_counts[i])   # first of the smallest
+            self.worker_assignments[event.worker_id] = shard
+            self.worker_counts[shard] += 1
+        self.shards[shard].apply_event(event)
+
+    def remove_worker(self, worker: WorkerId) -> None:
+        shard = self.worker_assignments.pop(worker, None)
+        if shard is not None:
+            self.worker_counts[shard] -= 1
+            self.shards[shard].remove_worker(worker)
+
+    @staticmethod
+    def _merge(parts: Sequence[OverlapScores]) -> OverlapScores:
+        out = OverlapScores()
+        for k, p in enumerate(parts):
+            out.scores.update(p.scores)
+            if k == 0:
+                out.frequencies = list(p.frequencies)
+            else:
+                out.frequencies += [0] * (len(p.frequencies) - len(out.frequencies))
+                for i, f in enumerate(p.frequencies):
+                    out.frequencies[i] += f
+        return out
+
+    def find_matches_batch(self, sequences: Sequence[Sequence[int]]) -> List[OverlapScores]:
+        per_shard = [t.find_matches_batch(sequences, False) for t in self.shards]
+        return [self._merge([ps[i] for ps in per_shard]) for i in range(len(sequences))]
+
+    def find_matches(self, sequence: Sequence[int]) -> OverlapScores:
+        return self.find_matches_batch([list(sequence)])[0]
+
+    def find_matches_for_request(self, tokens) -> OverlapScores:
+        return self.find_matches_for_requests([tokens])[0]
+
+    def find_matches_for_requests(self, requests: Sequence) -> List[OverlapScores]:
+        from .tokens import hash_token_blocks
+        toks = [_as_u32(t) for t in requests]
+        offs = np.zeros(len(toks) + 1, dtype=np.int64)
+        offs[1:] = np.cumsum([t.size for t in toks])
+        flat = np.concatenate(toks) if toks else np.zeros(0, dtype=np.uint32)
+        boff, bh, _ = hash_token_blocks(flat, offs, self.kv_block_size, XXH3_SEED, chained=False)
+        hashes = bh if bh.size else np.zeros(1, dtype=np.uint64)
+        per_shard = [[t._to_overlap(row) for row in t.find_matches_device_arrays(hashes, boff, False)[0]]
+                     for t in self.shards]
+        return [self._merge([ps[i] for ps in per_shard]) for i in range(len(toks))]
+
+    def shutdown(self) -> None:
+        for t in self.shards:
+            t.close()

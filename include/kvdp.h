@@ -288,7 +288,8 @@ int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int6
                             int32_t early_exit, int32_t num_workers, uint32_t* d_scores, int32_t* d_matched_depth,
                             kvdp_stream_t stream);
 /* Introspection for tests: what = 0 nodes; 1 children of node `arg`; 2 lookup entries of worker `arg`; 3 workers on node
- * `arg`; 4 root's child for tokens hash `arg` (node id or -1); 5 workers with a lookup table. */
+ * `arg`; 4 root's child for tokens hash `arg` (node id or -1); 5 workers with a lookup table; 6 nodes whose worker set
+ * still holds slot `arg` (0 right after kvdp_index_remove_worker means the slot can serve another worker id). */
 int64_t kvdp_index_stat(kvdp_index* ix, int32_t what, uint64_t arg);
 
 /* ================================================================== §I. Engine-facing KV-event ABI

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 from dynamo_exp_b200.indexer import (KvCacheEvent, KvCacheEvents, KvCacheRemoveData, KvCacheStoreData,
-                                     KvCacheStoredBlockData, KvIndexer, RadixTree, RouterEvent)
+                                     KvCacheStoredBlockData, KvIndexer, KvIndexerSharded, RadixTree, RouterEvent)
 from oracle.radix_oracle import RadixTree as OracleTree
 from tests.util import tokens_for
 
@@ -179,3 +179,89 @@ def test_router_event_wire_format(gpu):
     assert back.events[0].data.blocks[0].block_hash == 2 and back.events[0].data.blocks[0].tokens_hash == 3
     big = RouterEvent(1, KvCacheEvent(2 ** 63, KvCacheStoreData(None, [KvCacheStoredBlockData(2 ** 64 - 1, 2 ** 63 + 5)])))
     assert RouterEvent.from_json(big.to_json()) == big
+
+
+def test_sharded_indexer_matches_sharded_oracle_with_100_workers(gpu):
+    """KvIndexerSharded (indexer.rs:677-884): workers bound to the emptiest shard at their first event, lookups merged
+    over shards. 100 workers over 3 shards (more than one 64-slot index can hold), removals and re-binding."""
+    rng = np.random.default_rng(5)
+    n_shards, n_workers = 3, 100
+    ix = KvIndexerSharded(n_shards, 16, max_nodes=1 << 14)
+    ref = [OracleTree() for _ in range(n_shards)]
+    assign, counts = {}, [0] * n_shards
+
+    def ref_shard(w):
+        if w not in assign:
+            s = min(range(n_shards), key=lambda i: counts[i])
+            assign[w] = s
+            counts[s] += 1
+        return assign[w]
+    docs = [[int(x) for x in rng.integers(1, 1 << 40, size=24)] for _ in range(12)]
+    eid = 0
+    for step in range(600):
+        w = int(rng.integers(0, n_workers))
+        r = rng.random()
+        if r < 0.75:
+            d = int(rng.integers(0, len(docs)))
+            depth = int(rng.integers(1, 24))
+            th = docs[d][:depth]
+            bh = [(h ^ (w << 48)) & (2 ** 64 - 1) for h in th]          # engine-side ids are per worker
+            ix.apply_event(RouterEvent(w, KvCacheEvent(eid, KvCacheStoreData(
+                None, [KvCacheStoredBlockData(b, t) for b, t in zip(bh, th)]))))
+            ref[ref_shard(w)].apply_stored(w, None, list(zip(bh, th)))
+        elif r < 0.93:
+            d = int(rng.integers(0, len(docs)))
+            k = int(rng.integers(0, 24))
+            victims = [(docs[d][k] ^ (w << 48)) & (2 ** 64 - 1)]
+            ix.apply_event(RouterEvent(w, KvCacheEvent(eid, KvCacheRemoveData(victims))))
+            ref[ref_shard(w)].apply_removed(w, victims)
+        else:
+            ix.remove_worker(w)
+            if w in assign:
+                s = assign.pop(w)
+                counts[s] -= 1
+                ref[s].remove_worker(w)
+        eid += 1
+    assert ix.worker_assignments == assign and ix.worker_counts == counts
+    queries = [d[:int(rng.integers(1, 25))] for d in docs] + [[7, 8, 9]]
+    got = ix.find_matches_batch(queries)
+    for q, g in zip(queries, got):
+        want = {}
+        for t in ref:
+            want.update({w: c for w, c in t.find_matches(q, False).items() if c})
+        assert g.scores == want
+    assert len({w for g in got for w in g.scores}) > 64             # more workers than one index could hold
+    ix.shutdown()
+
+
+def test_worker_slots_are_recycled_when_nothing_stale_is_left(gpu):
+    """One index serves any number of worker ids over its lifetime as long as at most 64 are alive at once; a removed
+    worker that left a stale membership behind (overwritten lookup entry, indexer.rs:380-386) keeps its slot."""
+    trie, ref = RadixTree(max_nodes=1 << 12), OracleTree()
+    for w in range(1000, 1300):                      # 300 distinct ids, one after the other
+        ev = store_event(w, 1, [1, 2, w])
+        trie.apply_event(ev)
+        ref.apply_stored(w, None, [(i * 100, i) for i in [1, 2, w]])
+        assert trie.find_matches([1, 2, w], False).scores == {w: 3}
+        trie.remove_worker(w)
+        ref.remove_worker(w)
+    assert trie.find_matches([1, 2, 1299], False).scores == {}
+    # a stale membership: worker 7 re-uses external hash 700 for a block that another worker already created under
+    # the root, so its lookup entry for 700 moves to that node and the first node is never visited by remove_worker
+    def both(worker, parent, blocks):
+        trie.apply_event(RouterEvent(worker, KvCacheEvent(1, KvCacheStoreData(
+            parent, [KvCacheStoredBlockData(b, t) for b, t in blocks]))))
+        ref.apply_stored(worker, parent, blocks)
+    both(8, None, [(900, 9)])
+    both(7, None, [(700, 5)])
+    both(7, None, [(700, 9)])
+    trie.remove_worker(7)
+    ref.remove_worker(7)
+    for q in ([5], [9], [5, 9]):
+        assert trie.find_matches(q, False).scores == {w: c for w, c in ref.find_matches(q, False).items() if c}
+    assert trie.find_matches([5], False).scores == {7: 1}          # the stale block still reports worker 7
+    assert 7 in trie._slot and trie.stat(6, trie._slot[7]) == 1   # ... so its slot is not handed out again
+    assert 8 in trie._slot
+    trie.remove_worker(8)
+    assert 8 not in trie._slot
+    trie.close()
