@@ -201,6 +201,7 @@ int copy_stream_create(CopyStream** stream, int num_layers, int num_blocks) {
 
 int copy_stream_destroy(CopyStream* cs) {
   if (!cs) return 0;
+  DeviceGuard g(cs->device);
   if (cs->stream) cudaStreamSynchronize(cs->stream);
   cs->ids.destroy();
   if (cs->stream) cudaStreamDestroy(cs->stream);
@@ -212,6 +213,7 @@ int copy_stream_prepare_block_ids(CopyStream* cs, int* src_block_ids, int* dst_b
   if (!cs || !cs->ok) return fail((int)cudaErrorInvalidValue, "copy_stream_prepare_block_ids: unusable handle");
   if (num_blocks < 0 || (num_blocks > 0 && (!src_block_ids || !dst_block_ids)))
     return fail((int)cudaErrorInvalidValue, "copy_stream_prepare_block_ids: bad id arrays");
+  DeviceGuard g(cs->device);  // the handle's stream lives on the device that was current at create time
   cs->h_src.assign(src_block_ids, src_block_ids + num_blocks);
   cs->h_dst.assign(dst_block_ids, dst_block_ids + num_blocks);
   cs->num_blocks = num_blocks;
@@ -222,6 +224,7 @@ int copy_stream_prepare_block_ids(CopyStream* cs, int* src_block_ids, int* dst_b
 int copy_stream_launch(CopyStream* cs, const void* src_data, void* dst_data, int prefix_dim, int suffix_dim,
                        int elem_size, int src_block_dim, int dst_block_dim) {
   if (!cs || !cs->ok) return fail((int)cudaErrorInvalidValue, "copy_stream_launch: unusable handle");
+  DeviceGuard g(cs->device);
   if (int rc = copy_blocks_launcher_3d(src_data, dst_data, cs->ids.d_src(), cs->ids.d_dst(), cs->num_blocks,
                                        prefix_dim, suffix_dim, elem_size, src_block_dim, dst_block_dim, cs->stream))
     return rc;
@@ -231,6 +234,7 @@ int copy_stream_launch(CopyStream* cs, const void* src_data, void* dst_data, int
 int copy_stream_memcpy(CopyStream* cs, const void* src_data, void* dst_data, int prefix_dim, int suffix_dim,
                        int elem_size, int src_block_dim, int dst_block_dim) {
   if (!cs || !cs->ok) return fail((int)cudaErrorInvalidValue, "copy_stream_memcpy: unusable handle");
+  DeviceGuard g(cs->device);
   if (int rc = validate_3d(src_data, dst_data, cs->h_src.data(), cs->h_dst.data(), cs->num_blocks, prefix_dim,
                            suffix_dim, elem_size, "copy_stream_memcpy"))
     return rc;
@@ -248,6 +252,7 @@ int copy_stream_memcpy(CopyStream* cs, const void* src_data, void* dst_data, int
 
 int copy_stream_sync(CopyStream* cs) {
   if (!cs || !cs->stream) return fail((int)cudaErrorInvalidValue, "copy_stream_sync: unusable handle");
+  DeviceGuard g(cs->device);
   KVDP_CUDA(cudaStreamSynchronize(cs->stream));
   return 0;
 }
@@ -274,6 +279,7 @@ int copy_stream_scatter(CopyStream* cs, const void* src_data, void* dst_data, co
     return -4;
   }
   if (!cs || !cs->ok || !src_data || !dst_data) return -5;
+  DeviceGuard g(cs->device);
   const uint64_t bs = dims[2], sf = dims[3];
   const uint64_t run = (uint64_t)dims[4] * dims[5] * elem_size;
   const uint64_t chunk = bs * sf * run;

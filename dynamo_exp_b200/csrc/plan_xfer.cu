@@ -114,12 +114,16 @@ int plan_build(kvdp_plan** out, const kvdp_plan_desc& d) {
   p->h_dst.assign(d.dst_layer_ptrs, d.dst_layer_ptrs + n_dst);
 
   bool host = false, pageable = false, h, pg;
-  pointer_is_host(p->h_src[0], &h, &pg);
-  host |= h;
-  pageable |= pg;
-  pointer_is_host(p->h_dst[0], &h, &pg);
-  host |= h;
-  pageable |= pg;
+  for (uint64_t ptr : p->h_src) {  // every slab is looked at: layers may come from different allocations
+    pointer_is_host(ptr, &h, &pg);
+    host |= h;
+    pageable |= pg;
+  }
+  for (uint64_t ptr : p->h_dst) {
+    pointer_is_host(ptr, &h, &pg);
+    host |= h;
+    pageable |= pg;
+  }
   p->host_memory = host;
   if (pageable) {
     delete p;
@@ -399,6 +403,9 @@ int kvdp_xfer_run(kvdp_xfer* x, const kvdp_plan* plan, const int32_t* h_src_ids,
   if (!x || !plan) return fail(KVDP_EINVAL, "kvdp_xfer_run: NULL handle");
   if (num_pairs < 0) return fail(KVDP_EINVAL, "kvdp_xfer_run: negative num_pairs");
   if (num_pairs > 0 && (!h_src_ids || !h_dst_ids)) return fail(KVDP_EINVAL, "kvdp_xfer_run: NULL id array");
+  if (plan->device != x->device)
+    return fail(KVDP_EINVAL, "kvdp_xfer_run: the plan was built for device %d, the engine runs on device %d",
+                plan->device, x->device);
   if (int rc = check_ids(plan, h_src_ids, h_dst_ids, num_pairs, flags)) return rc;
   DeviceGuard g(x->device);
   if (num_pairs > 0)
