@@ -265,6 +265,48 @@ def host_tier_bench(torch, lib):
             "staging": "2 x 32 blocks (2 x 256 MiB HBM), one DMA per request range, gather/scatter kernel per slot"}
 
 
+def token_transfer_bench(torch, lib, steps=10):
+    """token-granular transfer, the fused form of the NCCL connector's per-layer gather +
+    send + reshape_and_cache. Llama-3-8B shape, 8 requests x 4096 tokens scattered over 64 Ki slots, every layer, K and
+    V, 2 KiB rows (8 heads x 128 x bf16) in ONE launch; device to device on one GPU (HBM-bound: read + write)."""
+    from dynamo_exp_b200.transfer import token_rows_plan
+    L = lib.lib()
+    row, slots, ntok = 8 * 128 * 2, 1024 * 64, 8 * 4096
+    src = [torch.empty(2 * slots * row, dtype=torch.uint8, device="cuda").random_(0, 256) for _ in range(L8B)]
+    dst = [torch.zeros(2 * slots * row, dtype=torch.uint8, device="cuda") for _ in range(L8B)]
+    plan = token_rows_plan([t.data_ptr() for t in src], [t.data_ptr() for t in dst], slots, slots, row, row, row)
+    g = torch.Generator(device="cpu").manual_seed(9)
+    s_ids = torch.randperm(slots, generator=g)[:ntok].to(torch.int32).cuda()
+    d_ids = torch.randperm(slots, generator=g)[:ntok].to(torch.int32).cuda()
+    st = torch.cuda.Stream()
+
+    def run():
+        lib.check(L.kvdp_plan_launch(plan.handle, s_ids.data_ptr(), d_ids.data_ptr(), ntok, 0, L8B,
+                                     C.c_void_p(st.cuda_stream)))
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(st)
+    for _ in range(steps):
+        run()
+    b.record(st)
+    torch.cuda.synchronize()
+    sec = a.elapsed_time(b) / 1e3 / steps
+    for layer in (0, L8B - 1):          # spot check: K and V rows of a few tokens
+        for kv in (0, 1):
+            for i in (0, ntok // 2, ntok - 1):
+                so = (kv * slots + int(s_ids[i])) * row
+                do = (kv * slots + int(d_ids[i])) * row
+                if not torch.equal(src[layer][so:so + row], dst[layer][do:do + row]):
+                    raise RuntimeError("token transfer mismatch")
+    payload = ntok * row * 2 * L8B
+    plan.close()
+    return {"payload_GBps": payload / sec / GB, "hbm_GBps_read_plus_write": 2 * payload / sec / GB,
+            "tokens_per_s": ntok / sec, "ms_per_launch": sec * 1e3, "tokens": ntok, "run_bytes": row,
+            "runs_per_launch": ntok * 2 * L8B}
+
+
 def event_publish_bench(lib, n_events=20000, blocks_per_event=4, bs=64):
     """the engine-facing event ABI. One engine thread publishes stored events (4 full 64-token blocks
     each, chained parents) as fast as it can; the publisher thread hashes whatever queued up per GPU batch and applies
@@ -550,6 +592,8 @@ def run_single(args):
         line["hashes_per_s"] = line["hash"]["hashes_per_s"]
         line["router_index"] = router_index_bench(torch, lib)
         line["event_publish"] = event_publish_bench(lib)
+        line["token_transfer"] = token_transfer_bench(torch, lib)
+        torch.cuda.empty_cache()
     if not args.no_cpu:
         from oracle import kvoracle as ko
         threads = ko.hw_threads()

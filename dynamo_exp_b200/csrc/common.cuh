@@ -25,7 +25,7 @@ int fail(int code, const char* fmt, ...);  // records the message, returns code
 
 // ---------------------------------------------------------------- options (kvdp_set_option)
 struct Options {
-  int64_t copy_path = 0;    // 0 auto, 1 vector ld/st, 2 TMA load + vector store, 3 TMA load + TMA store
+  int64_t copy_path = 0;    // 0 auto, 1 vector ld/st, 2 TMA load + vector store, 3 TMA load + TMA store, 4 small chunks
   int64_t tile_bytes = 0;   // 0 = default per path
   int64_t stages = 0;       // 0 = default per path
   int64_t ctas_per_sm = 0;  // 0 = default per path

@@ -75,7 +75,7 @@ int kvdp_set_option(const char* name, int64_t value) {
   if (!name) return fail(KVDP_EINVAL, "kvdp_set_option: NULL name");
   Options& o = options();
   if (!strcmp(name, "copy_path")) {
-    if (value < 0 || value > 3) return fail(KVDP_EINVAL, "copy_path must be 0..3");
+    if (value < 0 || value > 4) return fail(KVDP_EINVAL, "copy_path must be 0..4");
     o.copy_path = value;
   } else if (!strcmp(name, "tile_bytes")) {
     if (value < 0 || value > 200 * 1024) return fail(KVDP_EINVAL, "tile_bytes out of range");

@@ -167,6 +167,57 @@ __global__ void __launch_bounds__(kVecThreads) kvdp_copy_vec_kernel(const __grid
   publish_done(a);
 }
 
+// ------------------------------------------------------------------------------------------------ path 4
+// Small chunks (token-granular rows, <= 4 KiB per (layer, K|V, pair)): a CTA per chunk would leave most threads idle
+// and pay the index decode and two dependent id / table loads once per chunk. Here a GROUP of lanes (a whole warp for
+// 2-4 KiB, down to 4 lanes for <= 256 B, so that a lane has about kSmallVecs vectors per chunk) owns kSmallChunks
+// chunks at a time: it decodes them together, then every lane has up to kSmallChunks * kSmallVecs loads in flight
+// before the first store. Lanes of a group touch consecutive vectors: full-line accesses.
+constexpr int kSmallChunks = 4;
+constexpr int kSmallVecs = 4;
+constexpr uint32_t kSmallChunkMax = 4096;
+template <int VEC, bool CONTIG, bool SRC_STRIDED>
+__global__ void __launch_bounds__(kVecThreads) kvdp_copy_small_kernel(const __grid_constant__ CopyArgs a) {
+  using V = typename VecT<VEC>::T;
+  const uint32_t G = a.group_lanes;
+  const uint32_t gl = threadIdx.x & (G - 1);  // lane inside the group
+  const int64_t groups_total = (int64_t)gridDim.x * (kVecThreads / G);
+  const int64_t group = (int64_t)blockIdx.x * (kVecThreads / G) + threadIdx.x / G;
+  const uint32_t nvec = a.chunk_bytes / VEC;  // tiles_per_chunk == 1: every tile is a whole chunk
+  for (int64_t c0 = group * kSmallChunks; c0 < a.total_tiles; c0 += groups_total * kSmallChunks) {
+    TileCoord t[kSmallChunks];
+    uint64_t base0[kSmallChunks];
+#pragma unroll
+    for (int u = 0; u < kSmallChunks; ++u) {
+      if (c0 + u < a.total_tiles) {
+        t[u] = decode_tile(a, c0 + u);
+        base0[u] = dst_base(a, t[u].layer, 0);
+      }
+    }
+    for (uint32_t v0 = gl; v0 < nvec; v0 += G * kSmallVecs) {
+      V regs[kSmallChunks][kSmallVecs];
+#pragma unroll
+      for (int u = 0; u < kSmallChunks; ++u) {
+#pragma unroll
+        for (int k = 0; k < kSmallVecs; ++k) {
+          const uint32_t v = v0 + k * G;
+          if (c0 + u < a.total_tiles && v < nvec)
+            regs[u][k] = ld_vec<VEC>(SRC_STRIDED ? src_addr_strided(a, t[u], v * VEC) : t[u].src + (size_t)v * VEC);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kSmallChunks; ++u) {
+#pragma unroll
+        for (int k = 0; k < kSmallVecs; ++k) {
+          const uint32_t v = v0 + k * G;
+          if (c0 + u < a.total_tiles && v < nvec) st_vec<VEC>(dst_addr<CONTIG>(a, t[u], base0[u], v * VEC), regs[u][k]);
+        }
+      }
+    }
+  }
+  publish_done(a);
+}
+
 // ------------------------------------------------------------------------------------------------ path 2
 // smem: [stages][tile_bytes] ring, then `stages` full-barriers. Thread 0 keeps `stages` bulk loads in flight.
 template <bool CONTIG>
@@ -287,6 +338,17 @@ int set_smem(K kernel, size_t bytes) {
 }
 
 template <int VEC>
+int launch_small(const CopyArgs& a, bool contig, int grid, cudaStream_t stream) {
+  if (a.src_row_stride != 0)
+    kvdp_copy_small_kernel<VEC, false, true><<<grid, kVecThreads, 0, stream>>>(a);
+  else if (contig)
+    kvdp_copy_small_kernel<VEC, true, false><<<grid, kVecThreads, 0, stream>>>(a);
+  else
+    kvdp_copy_small_kernel<VEC, false, false><<<grid, kVecThreads, 0, stream>>>(a);
+  return 0;
+}
+
+template <int VEC>
 int launch_vec(const CopyArgs& a, bool contig, int grid, cudaStream_t stream) {
   if (a.src_row_stride != 0)
     kvdp_copy_vec_kernel<VEC, false, true><<<grid, kVecThreads, 0, stream>>>(a);
@@ -337,9 +399,12 @@ int launch_strided_copy(CopyArgs a, uint32_t align, const CopyLaunchHints& hints
       a.row_groups == 1 && a.dst_col_offset == 0 && (a.rows == 1 || a.dst_row_stride == (int64_t)a.run_bytes);
   int path = (int)opt.copy_path;
   const bool host_tma = hints.host_memory && opt.host_path == 2;
-  if (align < 16 || (hints.host_memory && !host_tma) || a.src_row_stride != 0) path = 1;
+  const bool must_vec = align < 16 || (hints.host_memory && !host_tma) || a.src_row_stride != 0;
+  const bool small_ok = a.chunk_bytes <= kSmallChunkMax && !hints.host_memory;
   a.l2_hint = (uint32_t)opt.l2_hint;
-  if (path == 0) path = contig ? 3 : 2;
+  if (path == 4 && !small_ok) path = 0;
+  if (must_vec && path != 4) path = (small_ok && opt.copy_path == 0) ? 4 : 1;
+  if (path == 0) path = small_ok ? 4 : (contig ? 3 : 2);
   if (path == 3 && !contig) path = 2;
 
   // tile geometry: tiles are contiguous source slices; a tile is a whole number of vectors and, on the
@@ -348,7 +413,8 @@ int launch_strided_copy(CopyArgs a, uint32_t align, const CopyLaunchHints& hints
   if (tile == 0) tile = (path == 1) ? 32768u : 16384u;
   tile = std::max(tile, 1024u) & ~1023u;
   if (tile > a.chunk_bytes) tile = a.chunk_bytes;  // small chunks: one tile each
-  if (path != 1 && (tile % 16) != 0) path = 1;
+  if (path == 4) tile = a.chunk_bytes;
+  if ((path == 2 || path == 3) && (tile % 16) != 0) path = 1;
   a.tile_bytes = tile;
   a.tiles_per_chunk = (a.chunk_bytes + tile - 1) / tile;
   a.total_tiles = (int64_t)a.layers_run * a.prefix_dim * a.num_pairs * a.tiles_per_chunk;
@@ -370,6 +436,23 @@ int launch_strided_copy(CopyArgs a, uint32_t align, const CopyLaunchHints& hints
       case 4: launch_vec<4>(a, contig, grid, stream); break;
       case 2: launch_vec<2>(a, contig, grid, stream); break;
       default: launch_vec<1>(a, contig, grid, stream); break;
+    }
+  } else if (path == 4) {
+    if (ctas_per_sm <= 0) ctas_per_sm = 2;
+    const uint32_t nvec = a.chunk_bytes / align;
+    uint32_t G = 32;
+    while (G > 4 && nvec <= (G / 2) * kSmallVecs) G >>= 1;
+    a.group_lanes = G;
+    const int64_t groups_needed = (a.total_tiles + kSmallChunks - 1) / kSmallChunks;
+    const int64_t per_cta = kVecThreads / G;
+    grid64 = std::min<int64_t>((int64_t)di.sm_count * ctas_per_sm, (groups_needed + per_cta - 1) / per_cta);
+    const int grid = (int)std::max<int64_t>(grid64, 1);
+    switch (align) {
+      case 16: launch_small<16>(a, contig, grid, stream); break;
+      case 8: launch_small<8>(a, contig, grid, stream); break;
+      case 4: launch_small<4>(a, contig, grid, stream); break;
+      case 2: launch_small<2>(a, contig, grid, stream); break;
+      default: launch_small<1>(a, contig, grid, stream); break;
     }
   } else if (path == 2) {
     int stages = (int)opt.stages;

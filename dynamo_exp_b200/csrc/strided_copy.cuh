@@ -29,6 +29,7 @@ struct CopyArgs {
   int64_t src_row_stride, src_col_offset;
   uint32_t tile_bytes;
   uint32_t l2_hint;  // path 3: bit 0 = evict_first on loads, bit 1 = on stores
+  uint32_t group_lanes;  // path 4: lanes that share one chunk (4, 8, 16 or 32)
   uint32_t tiles_per_chunk;
   int64_t total_tiles;
   // optional completion signal (last CTA to finish publishes *done_flag = done_value at system scope)

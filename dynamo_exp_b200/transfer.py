@@ -290,6 +290,66 @@ def gather_token_rows(cache_ptr: int, out_ptr: int, slot_mapping, num_slots: int
             eng.close()
 
 
+def token_rows_plan(src_layer_ptrs: Sequence[int], dst_layer_ptrs: Sequence[int], src_num_slots: int,
+                    dst_num_slots: int, src_row_bytes: int, dst_row_bytes: int, col_bytes: int, src_col_offset: int = 0,
+                    dst_col_offset: int = 0, device: int = -1) -> CopyPlan:
+    """The copy plan behind `transfer_token_rows`: token slots play the part of blocks, K|V is the prefix, one run of
+    `col_bytes` per (layer, K|V, token)."""
+    src, dst = _u64(src_layer_ptrs), _u64(dst_layer_ptrs)
+    d = _lib.PlanDesc()
+    d.num_layers, d.row_groups, d.prefix_dim, d.rows = len(src), 1, 2, 1
+    d.run_bytes = col_bytes
+    d.src_prefix_stride, d.src_block_stride = int(src_num_slots) * src_row_bytes, src_row_bytes
+    if src_col_offset:                      # a head slice of the source row; whole rows are plain contiguous runs
+        d.src_row_stride, d.src_col_offset = src_row_bytes, src_col_offset
+    d.dst_prefix_stride, d.dst_block_stride = int(dst_num_slots) * dst_row_bytes, dst_row_bytes
+    d.dst_row_stride, d.dst_col_offset = dst_row_bytes, dst_col_offset
+    d.src_blocks, d.dst_blocks = int(src_num_slots), int(dst_num_slots)
+    d.src_layer_ptrs, d.dst_layer_ptrs, d.device = src.ctypes.data, dst.ctypes.data, device
+    return CopyPlan.from_desc(d, keepalive=(src, dst))
+
+
+def transfer_token_rows(src_layer_ptrs: Sequence[int], dst_layer_ptrs: Sequence[int], src_slots, dst_slots,
+                        src_num_slots: int, dst_num_slots: int, src_row_bytes: int, dst_row_bytes: int,
+                        col_bytes: Optional[int] = None, src_col_offset: int = 0, dst_col_offset: int = 0,
+                        engine: Optional[TransferEngine] = None, device: int = -1) -> None:
+    """Token-granular prefill -> decode transfer in ONE launch over all layers, K and V:
+
+        dst[l][kv][dst_slots[i]][dst_col_offset : +col_bytes] = src[l][kv][src_slots[i]][src_col_offset : +col_bytes]
+
+    for caches laid out `[2, num_slots, row_bytes]` per layer (vLLM's `[2, num_blocks, block_size, H, D]` viewed per
+    token slot). This is the whole per-request data path of the reference's NCCL connector — per layer a torch gather
+    `cache.reshape(-1, H, D)[slot_mapping, h0:h1]`, a `cat`, three NCCL sends and, on the other side,
+    `reshape_and_cache_flash` (patch:1602-1672, 1676-1766) — with the head slice (TP resharding) folded into the column
+    offsets. The destination pointers may be peer-mapped (kvdp_ipc_import): the stores then go over NVLink."""
+    s_slots = np.asarray(src_slots, dtype=np.int64)
+    d_slots = np.asarray(dst_slots, dtype=np.int64)
+    if s_slots.shape != d_slots.shape:
+        raise KvError("src_slots and dst_slots must have the same length")
+    if s_slots.size == 0:
+        return
+    if np.any(s_slots < 0) or np.any(s_slots >= src_num_slots) or np.any(d_slots < 0) or np.any(d_slots >= dst_num_slots):
+        raise KvError("slot outside the cache")
+    if len(src_layer_ptrs) != len(dst_layer_ptrs) or not len(src_layer_ptrs):
+        raise KvError("need one source and one destination pointer per layer")
+    col_bytes = min(src_row_bytes - src_col_offset, dst_row_bytes - dst_col_offset) if col_bytes is None else col_bytes
+    if (col_bytes < 1 or src_col_offset < 0 or dst_col_offset < 0 or src_col_offset + col_bytes > src_row_bytes
+            or dst_col_offset + col_bytes > dst_row_bytes):
+        raise KvError("column range outside the row")
+    plan = token_rows_plan(src_layer_ptrs, dst_layer_ptrs, src_num_slots, dst_num_slots, src_row_bytes, dst_row_bytes,
+                           col_bytes, src_col_offset, dst_col_offset, device)
+    own = engine is None
+    eng = engine or TransferEngine(int(s_slots.size), device)
+    try:
+        eng.run(plan, s_slots.astype(np.int32), d_slots.astype(np.int32), num_layers=len(src_layer_ptrs),
+                check_dst_unique=True)
+        eng.sync()
+    finally:
+        plan.close()
+        if own:
+            eng.close()
+
+
 # ---------------------------------------------------------------------------------------------- raw memory helpers
 def memcpy_sync(dst: int, src: int, nbytes: int) -> None:
     _lib.check(_lib.lib().cuda_memcpy_sync(C.c_void_p(dst), C.c_void_p(src), int(nbytes)))

@@ -41,7 +41,8 @@ typedef void* kvdp_stream_t;
 const char* kvdp_last_error(void);
 /* major*10000 + minor*100 + patch */
 int kvdp_version(void);
-/* tunables: "copy_path" (0 auto, 1 vector ld/st, 2 TMA-load + vector store, 3 TMA load + TMA store),
+/* tunables: "copy_path" (0 auto, 1 vector ld/st, 2 TMA-load + vector store, 3 TMA load + TMA store, 4 warp-per-chunk
+ * vectors for chunks <= 4 KiB),
  * "tile_bytes", "stages", "ctas_per_sm", "host_path" (pinned memory: 0 vector kernel, 1 DMA loop, 2 TMA kernel), "host_ctas", "l2_hint". Returns KVDP_EINVAL for
  * unknown names. Intended for benchmarking; defaults are what the tests run. */
 int kvdp_set_option(const char* name, int64_t value);

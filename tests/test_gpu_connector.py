@@ -11,6 +11,7 @@ import numpy as np
 import pytest
 
 from dynamo_exp_b200.connector import DynamoKvdpConnector, KvdpMetadata, tp_targets
+from dynamo_exp_b200._lib import KvdpError
 from dynamo_exp_b200.storage import KvError
 from tests.util import DevBuf
 
@@ -223,3 +224,40 @@ def test_token_granular_paged_write_and_gather(gpu, H, D, E):
     assert np.array_equal(out.download().reshape(sel.size, -1), want)
     with pytest.raises(KvError):
         gather_token_rows(ck.ptr, out.ptr, [num_blocks * bs], num_blocks * bs, row)
+
+
+@pytest.mark.parametrize("L,Hs,Hd,D,E,h_src,h_dst,nh", [
+    (3, 8, 8, 16, 2, 0, 0, 8),      # same TP degree: whole rows
+    (2, 8, 2, 16, 2, 4, 0, 2),      # prefill TP1 -> decode TP4, decode rank 2 takes heads [4, 6)
+    (2, 2, 8, 8, 2, 0, 6, 2),       # prefill TP4 rank 3 -> decode TP1: its 2 heads land at heads [6, 8)
+    (1, 3, 5, 5, 1, 1, 2, 2),       # odd sizes: byte-granular runs, unaligned offsets
+])
+def test_token_granular_transfer_all_layers_one_launch(gpu, L, Hs, Hd, D, E, h_src, h_dst, nh):
+    """The fused form of the reference's NCCL connector data path (patch:1602-1672, 1676-1766): for every layer, K
+    and V, `dst.reshape(2, -1, Hd, D)[kv, dst_slots, h_dst:h_dst+nh] = src.reshape(2, -1, Hs, D)[kv, src_slots,
+    h_src:h_src+nh]`, against numpy indexing; untouched destination bytes must stay as they were."""
+    from dynamo_exp_b200.transfer import transfer_token_rows
+    rng = np.random.Generator(np.random.PCG64(L * 1000 + Hs * 10 + Hd))
+    ns_src, ns_dst, ntok = 40, 56, 23
+    srow, drow = Hs * D * E, Hd * D * E
+    src_np = [rng.integers(0, 255, size=(2, ns_src, srow), dtype=np.uint8) for _ in range(L)]
+    dst_np = [rng.integers(0, 255, size=(2, ns_dst, drow), dtype=np.uint8) for _ in range(L)]
+    src = [DevBuf(gpu, a.nbytes) for a in src_np]
+    dst = [DevBuf(gpu, a.nbytes) for a in dst_np]
+    for b, a in zip(src + dst, src_np + dst_np):
+        b.upload(a)
+    s_slots = rng.permutation(ns_src)[:ntok]
+    d_slots = rng.permutation(ns_dst)[:ntok]
+    transfer_token_rows([b.ptr for b in src], [b.ptr for b in dst], s_slots, d_slots, ns_src, ns_dst, srow, drow,
+                        col_bytes=nh * D * E, src_col_offset=h_src * D * E, dst_col_offset=h_dst * D * E)
+    for layer in range(L):
+        want = dst_np[layer].copy().reshape(2, ns_dst, Hd, D * E)
+        want[:, d_slots, h_dst:h_dst + nh] = src_np[layer].reshape(2, ns_src, Hs, D * E)[:, s_slots, h_src:h_src + nh]
+        assert np.array_equal(dst[layer].download().reshape(2, ns_dst, Hd, D * E), want), layer
+    with pytest.raises(KvdpError) as dup:                                                           # duplicate dst
+        transfer_token_rows([src[0].ptr], [dst[0].ptr], [0, 1], [5, 5], ns_src, ns_dst, srow, drow)
+    assert dup.value.code == -73
+    with pytest.raises(KvError):
+        transfer_token_rows([src[0].ptr], [dst[0].ptr], [0], [ns_dst], ns_src, ns_dst, srow, drow)
+    with pytest.raises(KvError):
+        transfer_token_rows([src[0].ptr], [dst[0].ptr], [0], [0], ns_src, ns_dst, srow, drow, col_bytes=drow + 1)

@@ -11,7 +11,7 @@ from tests.util import DevBuf, PinnedBuf, payload, permutation
 
 pytestmark = pytest.mark.gpu
 
-PATHS = [1, 2, 3]
+PATHS = [1, 2, 3, 4]   # 4 = lane-group-per-chunk kernel, taken when a chunk is <= 4 KiB (else the launcher falls back to auto)
 
 
 @pytest.fixture(autouse=True)

@@ -57,7 +57,7 @@ def run_reshard(gpu, oracle, src_tp, dst_tp, L, H, D, bs, E, Np, Nd, sid, did, p
             assert np.array_equal(got[:, did], want), (q, l)
 
 
-@pytest.mark.parametrize("path", [1, 2])
+@pytest.mark.parametrize("path", [1, 2, 4])
 @pytest.mark.parametrize("src_tp,dst_tp", [(1, 1), (1, 2), (1, 4), (2, 4), (1, 8), (2, 8), (4, 2), (4, 1), (8, 2),
                                            (2, 1), (8, 8)])
 def test_reshard_canonical_slice(gpu, oracle, src_tp, dst_tp, path):
@@ -70,6 +70,15 @@ def test_reshard_element_sizes_and_odd_head_dims(gpu, oracle, E, D):
     """Runs of 5..32 bytes: alignment drops below 16 and the narrow-vector path must stay exact."""
     run_reshard(gpu, oracle, 2, 4, L=2, H=8, D=D, bs=4, E=E, Np=5, Nd=5, sid=[4, 1], did=[0, 3], path=0)
     run_reshard(gpu, oracle, 4, 2, L=2, H=8, D=D, bs=4, E=E, Np=5, Nd=5, sid=[4, 1], did=[0, 3], path=0)
+
+
+@pytest.mark.parametrize("bs,D,E", [(1, 8, 2), (2, 16, 2), (4, 64, 2), (16, 32, 2), (3, 5, 1), (2, 128, 4)])
+def test_reshard_small_chunks_every_lane_group_width(gpu, oracle, bs, D, E):
+    """Chunks of 16 B .. 4 KiB take the lane-group kernel (4, 8, 16 or 32 lanes per chunk): scatter, gather and the
+    same-TP copy must stay exact for each width and for narrow vectors."""
+    for src_tp, dst_tp in ((1, 2), (2, 1), (2, 2), (1, 4)):
+        run_reshard(gpu, oracle, src_tp, dst_tp, L=3, H=4, D=D, bs=bs, E=E, Np=11, Nd=13,
+                    sid=[10, 0, 3, 6, 7, 1, 9], did=[2, 8, 0, 4, 12, 5, 6], path=0)
 
 
 def test_reshard_llama70b_tp4_to_tp2_shape(gpu, oracle):
