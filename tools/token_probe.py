@@ -50,6 +50,8 @@ def run(row, col, s_off, d_off, path, label):
     lib.check(L.kvdp_set_option(b"copy_path", 0))
 
 
+
+
 for path in (0, 1, 3, 4):
     run(2048, 2048, 0, 0, path, "2 KiB rows, whole row")
 for path in (0, 1, 4):
