@@ -74,10 +74,10 @@ def test_sequence_golden_vectors_on_gpu(gpu):
         assert [[str(int(a)), str(int(b))] for a, b in zip(bh, sh)] == s["blocks"], s["block_size"]
 
 
-@pytest.mark.parametrize("bs", [4, 11, 16, 32, 64, 128, 48, 1, 256, 300])
+@pytest.mark.parametrize("bs", [4, 8, 11, 16, 32, 64, 128, 48, 1, 256, 300])
 @pytest.mark.parametrize("salt", [0, 1337, 0x1234567890ABCDEF])
 def test_ragged_batch_vs_oracle(gpu, oracle, bs, salt):
-    """Ragged CSR batch incl. empty / sub-block / exact / +1 requests; fast TMA path for bs 64 and 128, generic else."""
+    """Ragged CSR batch incl. empty / sub-block / exact / +1 requests; TMA rows for bs 64 / 128 / 256, lane-parts kernel for bs 4 / 8 / 16 / 32, generic kernel else."""
     lens = [0, 1, bs - 1, bs, bs + 1, 2 * bs + 1, 0, 5 * bs, 3 * bs + bs // 2, 512, 1000, 33 * bs, 0]
     lens = [max(0, x) for x in lens]
     offs = np.zeros(len(lens) + 1, dtype=np.int64)
@@ -90,6 +90,22 @@ def test_ragged_batch_vs_oracle(gpu, oracle, bs, salt):
     assert np.array_equal(sh, w_sh)
     _, bh_only, none = hash_token_blocks(toks, offs, bs, salt, chained=False)
     assert np.array_equal(bh_only, w_bh) and none.size == 0
+
+
+@pytest.mark.parametrize("bs", [4, 8, 16, 32, 256])
+def test_short_and_1k_block_fast_paths_on_a_wide_batch(gpu, oracle, bs):
+    """Block sizes of 4..32 tokens take the lane-parts kernel (several lanes per block, many warps and CTAs with their
+    own block ranges), 256 tokens the 1 KiB TMA rows; 3000 ragged requests with aligned and unaligned starts."""
+    rng = np.random.Generator(np.random.PCG64(bs))
+    lens = rng.integers(0, 40 * bs, size=3000)
+    lens[rng.integers(0, lens.size, size=300)] = 0
+    lens[::7] = (lens[::7] // 4) * 4                       # some requests start on 16-byte boundaries, most do not
+    offs = np.zeros(lens.size + 1, dtype=np.int64)
+    offs[1:] = np.cumsum(lens)
+    toks = tokens_for(7, int(offs[-1]))
+    boff, bh, sh = hash_token_blocks(toks, offs, bs, 1337)
+    w_off, w_bh, w_sh = oracle.hash_batch(toks, offs, bs, 1337, threads=8)
+    assert np.array_equal(boff, w_off) and np.array_equal(bh, w_bh) and np.array_equal(sh, w_sh)
 
 
 def test_unaligned_request_starts_use_the_lane_fallback(gpu, oracle):

@@ -13,7 +13,7 @@ L = lib.lib()
 BS = 64
 
 
-def run(lens, chained, label, iters=20):
+def run(lens, chained, label, iters=20, BS=BS):
     lens = np.asarray(lens, dtype=np.int64)
     n_req = lens.size
     offs = np.zeros(n_req + 1, dtype=np.int64)
@@ -63,3 +63,7 @@ big = mix * 4
 run(big, True, "router mix x4, chained")
 run(sorted(big), True, "router mix x4 SORTED by length, chained")
 run(sorted(big), False, "router mix x4 SORTED by length, un-chained")
+
+for bs in (16, 32, 64, 128, 256):
+    run(mix, False, f"router mix, un-chained, block_size={bs}", BS=bs)
+    run(mix, True, f"router mix, chained, block_size={bs}", BS=bs)
