@@ -143,3 +143,63 @@ def test_host_tier_offload_onboard_round_trip(gpu, oracle, layout):
         tier2.onboard([0, 1], [2, 2])  # duplicate destination blocks
     tier.close()
     tier2.close()
+
+
+def test_host_tier_under_a_concurrent_copy_stream(gpu, oracle):
+    """offload / onboard while another stream keeps the SMs and HBM busy (here: a second engine running
+    block copies over unrelated caches, launch after launch, without synchronising) must not corrupt either side."""
+    layout = KvLayout.KvFirst
+    L, nb, nh = 4, 48, 48
+    bd = KvBlockDetails(layout, 16, KvModelDetails(L, 4, 32, DType.BF16))
+    chunk = bd.bytes_per_token_block_per_layer() // 2
+    dev = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    back = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    host = KvContiguousBlocks(nh, L, chunk, StorageType.Pinned)
+    src = []
+    for l, layer in enumerate(dev.layers):
+        data = payload(layer.storage_size(), 900 + l)
+        gpu.check(gpu.lib().cuda_memcpy_sync(layer.get_pointer(), data.ctypes.data, data.nbytes))
+        src.append(data)
+    # the busy neighbour: its own caches, its own stream
+    na = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    nbk = KvBlockStorage.allocate(nb, bd, StorageType.Device(0))
+    n_src = []
+    for l, layer in enumerate(na.layers):
+        data = payload(layer.storage_size(), 950 + l)
+        gpu.check(gpu.lib().cuda_memcpy_sync(layer.get_pointer(), data.ctypes.data, data.nbytes))
+        n_src.append(data)
+    n_plan = CopyPlan.block_copy(na, nbk)
+    n_eng = TransferEngine(nb)
+    n_sid, n_did = list(permutation(nb, 21)), list(permutation(nb, 22))
+    tier = HostTier(dev, host, staging_blocks=7)
+    tier_b = HostTier(back, host, staging_blocks=5)
+    dev_ids, host_ids, new_ids = list(permutation(nb, 23)), list(permutation(nh, 24)), list(permutation(nb, 25))
+    for _ in range(6):
+        n_eng.run(n_plan, n_sid, n_did, num_layers=L)          # queued, not waited for
+    tier.offload(dev_ids, host_ids)
+    for _ in range(6):
+        n_eng.run(n_plan, n_sid, n_did, num_layers=L)
+    tier.sync()
+    tier_b.onboard(host_ids, new_ids)
+    for _ in range(6):
+        n_eng.run(n_plan, n_sid, n_did, num_layers=L)
+    tier_b.sync()
+    n_eng.sync()
+    want_host = np.zeros(host.storage_size(), dtype=np.uint8)
+    oracle.relayout_contig(src, layout.value, nb, chunk, want_host, dev_ids, host_ids, True)
+    assert np.array_equal(host.storage.as_numpy(), want_host)
+    want_dev = [np.zeros_like(s) for s in src]
+    oracle.relayout_contig(want_dev, layout.value, nb, chunk, want_host, host_ids, new_ids, False)
+    for l, layer in enumerate(back.layers):
+        got = np.empty(layer.storage_size(), dtype=np.uint8)
+        gpu.check(gpu.lib().cuda_memcpy_sync(got.ctypes.data, layer.get_pointer(), got.nbytes))
+        assert np.array_equal(got, want_dev[l]), l
+    want_n = [np.zeros_like(s) for s in n_src]
+    oracle.copy_blocks_layers(n_src, want_n, n_sid, n_did, bd.prefix_dim(), nb, nb, bd.suffix_dim(), bd.elem_size())
+    for l, layer in enumerate(nbk.layers):
+        got = np.empty(layer.storage_size(), dtype=np.uint8)
+        gpu.check(gpu.lib().cuda_memcpy_sync(got.ctypes.data, layer.get_pointer(), got.nbytes))
+        assert np.array_equal(got, want_n[l]), l
+    tier.close()
+    tier_b.close()
+    n_eng.close()
