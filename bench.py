@@ -66,6 +66,32 @@ def parse_args():
     return ap.parse_args()
 
 
+def env_info(torch=None, device_index: int = 0) -> dict:
+    """Where the numbers came from: GPU, driver / CUDA / library versions, host cores and the synthetic-data seeds
+    (SURVEY D.3)."""
+    info = {"host_cores": os.cpu_count(), "seeds": {"tokens": "0xD15A66", "kv_payload": 42, "block_ids": 1234}}
+    try:
+        from dynamo_exp_b200 import _lib
+        info["libkvdp_version"] = int(_lib.lib().kvdp_version())
+    except Exception:
+        pass
+    if torch is not None:
+        try:
+            p = torch.cuda.get_device_properties(device_index)
+            info.update({"gpu": p.name, "sms": p.multi_processor_count, "hbm_GiB": round(p.total_memory / 2 ** 30, 1),
+                         "torch": torch.__version__, "cuda_runtime": torch.version.cuda})
+        except Exception:
+            pass
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        v = pynvml.nvmlSystemGetDriverVersion()
+        info["driver"] = v.decode() if isinstance(v, bytes) else v
+    except Exception:
+        pass
+    return info
+
+
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
     """Samples SM clock, power and throttle reasons through NVML (in-process, every 5 ms) while the timed region runs;

@@ -16,7 +16,7 @@ import json
 
 import numpy as np
 
-from bench import BLOCK_BYTES, BLOCKS_PER_REQ, CHUNK, GB, L8B, ClockSampler, workload_config
+from bench import BLOCK_BYTES, BLOCKS_PER_REQ, CHUNK, GB, L8B, ClockSampler, env_info, workload_config
 from bench_single import Setup
 
 NVLINK_PEAK_MEASURED = 770.0   # GB/s per direction per GPU, peer copy (B200_PROFILING.md)
@@ -270,7 +270,7 @@ def run_multi(args, rank, local_rank, world):
             "comparators": {"nccl_send_recv_GBps": nccl_value, "cuda_memcpy_peer_GBps": memcpy_value,
                             "steps": nsteps_c},
             "options": {k: lib.get_option(k) for k in ("copy_path", "tile_bytes", "stages", "ctas_per_sm")},
-            "gpu_launches": steps * len(modes), "clocks": clk,
+            "gpu_launches": steps * len(modes), "clocks": clk, "env": env_info(torch, local_rank),
             "e2e": e2e,
         }
         print(json.dumps(line), flush=True)

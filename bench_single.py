@@ -8,7 +8,7 @@ import time
 
 import numpy as np
 
-from bench import (BLOCK_BYTES, BLOCKS_PER_REQ, BS, CHUNK, ELEM, GB, H8B, D8B, L8B, ROOT, ClockSampler,
+from bench import (BLOCK_BYTES, BLOCKS_PER_REQ, BS, CHUNK, ELEM, GB, H8B, D8B, L8B, ROOT, ClockSampler, env_info,
                    cpu_hash_leg, cpu_relayout_leg, workload_config)
 
 
@@ -579,6 +579,7 @@ def run_single(args):
                      "frac_of_nominal_8TBps": 2 * payload / k_avg / GB / 8000.0},
         "gpu_launches": args.steps,
         "clocks": clk,
+        "env": env_info(torch, 0),
     }
     del setup
     torch.cuda.empty_cache()
