@@ -111,6 +111,7 @@ class RadixTree:
         h = C.c_void_p()
         _lib.check(_lib.lib().kvdp_index_create(C.byref(h), int(max_nodes), MAX_WORKERS, int(device)))
         self._h = h
+        self._device = int(device)
         self._slot: Dict[WorkerId, int] = {}
         self._worker_of_slot: List[Optional[WorkerId]] = [None] * MAX_WORKERS
 
@@ -182,26 +183,36 @@ class RadixTree:
             return np.zeros((0, nw), dtype=np.uint32), np.zeros(0, dtype=np.int32)
         hashes = np.ascontiguousarray(hashes, dtype=np.uint64)
         seq_offsets = np.ascontiguousarray(seq_offsets, dtype=np.int64)
-        bufs = [C.c_void_p() for _ in range(4)]
         sizes = [max(hashes.nbytes, 8), seq_offsets.nbytes, n_req * nw * 4, n_req * 4]
-        try:
-            for b, n in zip(bufs, sizes):
-                _lib.check(L.kvdp_device_alloc(C.byref(b), n, -1))
-            _lib.check(L.cuda_memcpy_sync(bufs[0], hashes.ctypes.data, hashes.nbytes))
-            _lib.check(L.cuda_memcpy_sync(bufs[1], seq_offsets.ctypes.data, seq_offsets.nbytes))
-            _lib.check(L.kvdp_index_find_matches(self._h, bufs[0], bufs[1], n_req, int(early_exit), nw, bufs[2], bufs[3],
-                                                 None))
-            stream = L.kvdp_index_stream(self._h)
-            scores = np.zeros((n_req, nw), dtype=np.uint32)
-            depth = np.zeros(n_req, dtype=np.int32)
-            _lib.check(L.cuda_memcpy_async(scores.ctypes.data, bufs[2], scores.nbytes, stream))
-            _lib.check(L.cuda_memcpy_async(depth.ctypes.data, bufs[3], depth.nbytes, stream))
-            _lib.check(L.kvdp_stream_synchronize(stream))
-        finally:
-            for b in bufs:
-                if b.value:
-                    L.kvdp_device_free(b)
+        bufs = self._scratch(sizes)
+        _lib.check(L.cuda_memcpy_sync(bufs[0], hashes.ctypes.data, hashes.nbytes))
+        _lib.check(L.cuda_memcpy_sync(bufs[1], seq_offsets.ctypes.data, seq_offsets.nbytes))
+        _lib.check(L.kvdp_index_find_matches(self._h, bufs[0], bufs[1], n_req, int(early_exit), nw, bufs[2], bufs[3],
+                                             None))
+        stream = L.kvdp_index_stream(self._h)
+        scores = np.zeros((n_req, nw), dtype=np.uint32)
+        depth = np.zeros(n_req, dtype=np.int32)
+        _lib.check(L.cuda_memcpy_async(scores.ctypes.data, bufs[2], scores.nbytes, stream))
+        _lib.check(L.cuda_memcpy_async(depth.ctypes.data, bufs[3], depth.nbytes, stream))
+        _lib.check(L.kvdp_stream_synchronize(stream))
         return scores, depth
+
+    def _scratch(self, sizes):
+        """Device buffers for a lookup, kept between calls and grown when a batch needs more (a lookup per request must
+        not pay four allocations)."""
+        L = _lib.lib()
+        if not hasattr(self, "_bufs"):
+            self._bufs = [[C.c_void_p(), 0] for _ in sizes]
+        for slot, need in zip(self._bufs, sizes):
+            if slot[1] < need:
+                if slot[0].value:
+                    _lib.check(L.kvdp_stream_synchronize(L.kvdp_index_stream(self._h)))
+                    L.kvdp_device_free(slot[0])
+                    slot[0], slot[1] = C.c_void_p(), 0
+                cap = max(int(need), 2 * slot[1], 4096)
+                _lib.check(L.kvdp_device_alloc(C.byref(slot[0]), cap, self._device))
+                slot[1] = cap
+        return [slot[0] for slot in self._bufs]
 
     def _to_overlap(self, row: np.ndarray) -> OverlapScores:
         out = OverlapScores()
@@ -219,6 +230,10 @@ class RadixTree:
 
     def close(self) -> None:
         if self._h is not None and self._h.value:
+            for slot in getattr(self, "_bufs", []):
+                if slot[0].value:
+                    _lib.lib().kvdp_device_free(slot[0])
+            self._bufs = []
             _lib.lib().kvdp_index_destroy(self._h)
             self._h = C.c_void_p()
 
