@@ -16,6 +16,8 @@ sys.path.insert(0, ROOT)
 
 from dynamo_exp_b200 import _lib  # noqa: E402
 from dynamo_exp_b200.connector import DynamoKvdpConnector, KvdpMetadata  # noqa: E402
+from dynamo_exp_b200.remote_prefill import (RemotePrefillParams, TransferTracker, collect_transfer_counters,  # noqa: E402
+                                            execute_memory_transfers, plan_memory_transfers)
 from tests.util import DevBuf, payload  # noqa: E402
 
 L, H, D, BS, E, NB = 2, 4, 16, 8, 2, 8
@@ -52,10 +54,10 @@ def main():
         c.register_kv_caches([b.ptr for b in bufs], shape=(2, NB, BS, H, D), element_size=E)
         meta = KvdpMetadata("decode", [c.get_agent_metadata()], [c.kv_caches_base_addr["decode"]], NB)
         publish(os.path.join(d, "decode.meta"), meta.encode())
-        notifs = []
+        tracker = TransferTracker(tensor_parallel_size=1)     # decode engine: one notification per TP worker
         t0 = time.time()
-        while "req-1" not in notifs:
-            notifs += c.get_new_notifs().get("0", [])
+        while "req-1" not in tracker.finished_prefills:
+            tracker.update(*collect_transfer_counters([c]))
             if time.time() - t0 > 120:
                 raise TimeoutError("no notification")
             time.sleep(0.005)
@@ -80,9 +82,15 @@ def main():
         c.register_kv_caches([b.ptr for b in src], shape=(2, NB, BS, H, D), element_size=E)
         meta = KvdpMetadata.decode(wait_for(os.path.join(d, "decode.meta")))
         c.add_remote_agent("decode", meta.agent_metadata, 1, meta.kv_caches_base_addr, meta.num_blocks)
-        c.write_blocks([5, 0, 7], [0, 0, 0], [1, 6, 2], "decode", "req-1")
+        # the engine's plan for a remote-decode request whose blocks were all computed here (patch:3188-3221) ...
+        params = RemotePrefillParams(is_remote_decode=True, decode_block_ids=[1, 6, 2], decode_engine_id="decode")
+        reqs = plan_memory_transfers("req-1", [5, 0, 7], [], [], params)
+        ran = []
+        execute_memory_transfers(c, reqs, run_model=lambda: ran.append(1))        # ... run as a worker step
         c.sync()
-        assert c.get_done_tranfers() == ["req-1"]
+        tracker = TransferTracker(tensor_parallel_size=1)
+        tracker.update(*collect_transfer_counters([c]))
+        assert ran == [1] and tracker.finished_transfers == {"req-1"}
         wait_for(os.path.join(d, "parent.ok"))
         # pull the same blocks back into a second local cache and compare with the originals
         back = [DevBuf(_lib, LAYER_BYTES, dev) for _ in range(L)]
