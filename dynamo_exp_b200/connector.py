@@ -64,6 +64,78 @@ class KvdpMetadata:
         return KvdpMetadata(d["engine_id"], list(d["agent_metadata"]), d["kv_caches_base_addr"], d["num_blocks"])
 
 
+# ---------------------------------------------------------------------------------------------- metadata exchange
+class DirKvClient:
+    """The two etcd calls `NixlMetadataStore` makes (`kv_create_or_validate`, `kv_get_prefix`), backed by a directory:
+    enough for engines on one box (where CUDA-IPC handles are valid anyway). A deployment passes its own client."""
+
+    def __init__(self, root: str):
+        self.root = root
+        os.makedirs(root, exist_ok=True)
+
+    def _path(self, key: str) -> str:
+        return os.path.join(self.root, key.replace("/", "__"))
+
+    def kv_create_or_validate(self, key: str, value: bytes) -> None:
+        path = self._path(key)
+        try:
+            fd = os.open(path + ".tmp%d" % os.getpid(), os.O_WRONLY | os.O_CREAT | os.O_EXCL, 0o600)
+        except FileExistsError:
+            raise KvError(f"key {key} is being written by someone else")
+        with os.fdopen(fd, "wb") as f:
+            f.write(value)
+        if os.path.exists(path):
+            existing = open(path, "rb").read()
+            os.remove(path + ".tmp%d" % os.getpid())
+            if existing != value:
+                raise KvError(f"a different value exists for {key}")
+            return
+        os.rename(path + ".tmp%d" % os.getpid(), path)
+
+    def kv_get_prefix(self, key: str) -> List[dict]:
+        pre = os.path.basename(self._path(key))
+        out = []
+        for name in sorted(os.listdir(self.root)):
+            if name.startswith(pre) and ".tmp" not in name:
+                out.append({"key": name.replace("__", "/"), "value": open(os.path.join(self.root, name), "rb").read()})
+        return out
+
+
+class KvdpMetadataStore:
+    """reference: `NixlMetadataStore` (examples/llm/utils/nixl.py:59-116): engines publish their metadata under
+    `<namespace>/nixl_metadata/<engine_id>` and look their peers up by engine id; lookups are cached. Synchronous; the
+    client only needs the two calls of `DirKvClient`."""
+    NIXL_METADATA_KEY = "nixl_metadata"
+
+    def __init__(self, namespace: str, client) -> None:
+        if client is None:
+            raise KvError("Cannot be used with static workers")
+        self._namespace = namespace
+        self._stored: set = set()
+        self._cached: Dict[str, KvdpMetadata] = {}
+        self._client = client
+        self._key_prefix = f"{namespace}/{KvdpMetadataStore.NIXL_METADATA_KEY}"
+
+    def put(self, engine_id: str, metadata: KvdpMetadata) -> None:
+        key = "/".join([self._key_prefix, engine_id])
+        try:
+            self._client.kv_create_or_validate(key, metadata.encode())
+        except Exception as e:                      # the reference only warns (nixl.py:83-84)
+            import warnings
+            warnings.warn(f"A different metadata exists for engine {engine_id}: {e}")
+        self._stored.add(engine_id)
+
+    def get(self, engine_id: str) -> KvdpMetadata:
+        if engine_id in self._cached:
+            return self._cached[engine_id]
+        key = "/".join([self._key_prefix, engine_id])
+        for item in self._client.kv_get_prefix(key):
+            meta = KvdpMetadata.decode(item["value"])
+            self._cached[engine_id] = meta
+            return meta
+        raise KvError(f"Error retrieving metadata for engine {engine_id}")
+
+
 def tp_targets(src_tp: int, dst_tp: int, src_rank: int) -> List[int]:
     """Ranks of the other engine that rank `src_rank` exchanges blocks with (patch:1427-1471 for dst_tp >= src_tp:
     `rank * tp_multiplier + i`; the dst_tp < src_tp direction is the inverse map)."""

@@ -81,3 +81,31 @@ def test_counters_and_engine_tracker_need_one_count_per_tp_worker():
     assert t.pending() == ({"r2": -1}, {"r9": -1})
     t.update({"r2": 1}, {"r9": 1})
     assert t.finished_prefills == {"r1", "r2"} and t.finished_transfers == {"r9"} and t.pending() == ({}, {})
+
+
+def test_metadata_store_like_nixl_metadata_store(tmp_path):
+    """examples/llm/utils/nixl.py:59-116: put under <namespace>/nixl_metadata/<engine>, cached get, a clashing put only
+    warns, an unknown engine raises."""
+    import warnings
+
+    import pytest
+
+    from dynamo_exp_b200.connector import DirKvClient, KvdpMetadata, KvdpMetadataStore
+    from dynamo_exp_b200.storage import KvError
+    client = DirKvClient(str(tmp_path))
+    a, b = KvdpMetadataStore("dynamo", client), KvdpMetadataStore("dynamo", client)
+    meta = KvdpMetadata("eng-1", [b"\x00\x01handle", b"\xff"], [[[4096, 8192]], [[12288, 16384]]], 77)
+    a.put("eng-1", meta)
+    a.put("eng-1", meta)                                            # same value: validated, no complaint
+    got = b.get("eng-1")
+    assert got == meta and b.get("eng-1") is got                     # second lookup comes from the cache
+    assert [i["key"] for i in client.kv_get_prefix("dynamo/nixl_metadata/")] == ["dynamo/nixl_metadata/eng-1"]
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        a.put("eng-1", KvdpMetadata("eng-1", [b"other"], [], 1))
+    assert w and "different metadata" in str(w[0].message)
+    assert KvdpMetadataStore("dynamo", client).get("eng-1") == meta  # the first value stays
+    with pytest.raises(KvError):
+        b.get("eng-2")
+    with pytest.raises(KvError):
+        KvdpMetadataStore("dynamo", None)
