@@ -85,7 +85,8 @@ class DirKvClient:
         with os.fdopen(fd, "wb") as f:
             f.write(value)
         if os.path.exists(path):
-            existing = open(path, "rb").read()
+            with open(path, "rb") as f:
+                existing = f.read()
             os.remove(path + ".tmp%d" % os.getpid())
             if existing != value:
                 raise KvError(f"a different value exists for {key}")
@@ -97,7 +98,8 @@ class DirKvClient:
         out = []
         for name in sorted(os.listdir(self.root)):
             if name.startswith(pre) and ".tmp" not in name:
-                out.append({"key": name.replace("__", "/"), "value": open(os.path.join(self.root, name), "rb").read()})
+                with open(os.path.join(self.root, name), "rb") as f:
+                    out.append({"key": name.replace("__", "/"), "value": f.read()})
         return out
 
 
