@@ -192,6 +192,55 @@ def run_multi(args, rank, local_rank, world):
         for p in host_ptrs:
             L.cuda_free_host(C.c_void_p(p))
 
+
+    # ---- token-granular transfer over NVLink: the same memory viewed per token slot, 2 KiB rows, all
+    # layers and K|V in one launch; the decode cache region is treated as 32 layer slabs of [2, n*64 slots, 2 KiB].
+    token = None
+    if not args.no_comparators:
+        from dynamo_exp_b200.transfer import token_rows_plan
+        row, slots, ntok = 2048, n * 64, 8 * 4096
+        layer_bytes = 2 * n * CHUNK
+        if is_prefill:
+            t_src, t_dst = [p.value for p in own_layers], [peer_cache.value + l * layer_bytes for l in range(L8B)]
+        else:
+            t_src, t_dst = peer_layers, [own_cache.value + l * layer_bytes for l in range(L8B)]
+        t_plan = token_rows_plan(t_src, t_dst, slots, slots, row, row, row, device=local_rank)
+        rng_t = np.random.Generator(np.random.PCG64(99 + partner if is_prefill else 99 + rank))
+        ts_ids = rng_t.permutation(slots)[:ntok].astype(np.int32)
+        td_ids = rng_t.permutation(slots)[:ntok].astype(np.int32)
+
+        def token_timed(mode, count):
+            runner = is_prefill if mode == "push" else not is_prefill
+            torch.cuda.synchronize()
+            dist.barrier()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            st = setup.stream if runner else wait_stream
+            a.record(st)
+            if runner:
+                for _ in range(count):
+                    seq["v"] += 1
+                    lib.check(L.kvdp_xfer_run(setup.xfer, t_plan.handle, ts_ids.ctypes.data, td_ids.ctypes.data, ntok, 0,
+                                              L8B, 0, peer_flag, seq["v"]))
+            else:
+                seq["v"] += count
+                lib.check(L.kvdp_stream_wait_flag(C.c_void_p(wait_stream.cuda_stream), flag_ptr, seq["v"]))
+            b.record(st)
+            torch.cuda.synchronize()
+            dist.barrier()
+            t = torch.tensor([a.elapsed_time(b) / 1e3], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        token = {"tokens_per_launch": ntok, "run_bytes": row, "runs_per_launch": ntok * 2 * L8B}
+        k_t = max(2, min(steps, 10))
+        for mode in modes:
+            token_timed(mode, 2)
+            sec_t = token_timed(mode, k_t)
+            per_dir = ntok * row * 2 * L8B * k_t / sec_t / GB * max(1, P // D)
+            token[mode] = {"per_direction_GBps": per_dir, "frac_of_nominal_900": per_dir / NVLINK_PEAK_NOMINAL,
+                           "tokens_per_s": P * ntok * k_t / sec_t}
+        t_plan.close()
+
     # ---- comparators: (i) local relayout into HBM staging + NCCL send/recv, (ii) plain peer memcpy of the payload
     nccl_value = memcpy_value = None
     nsteps_c = max(2, min(steps, 10))
@@ -271,7 +320,7 @@ def run_multi(args, rank, local_rank, world):
                             "steps": nsteps_c},
             "options": {k: lib.get_option(k) for k in ("copy_path", "tile_bytes", "stages", "ctas_per_sm")},
             "gpu_launches": steps * len(modes), "clocks": clk, "env": env_info(torch, local_rank),
-            "e2e": e2e,
+            "e2e": e2e, "token_transfer": token,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()
