@@ -506,3 +506,28 @@ def test_legacy_memcpy_falls_back_to_dma_for_pageable_memory(gpu, oracle):
     want = np.zeros(prefix * nd * suffix * elem, dtype=np.uint8)
     oracle.copy_blocks_3d(src_h, want, sid, did, prefix, ns, nd, suffix, elem)
     assert np.array_equal(dst.download(), want)
+
+
+def test_range_limits_are_reported_not_wrapped(gpu):
+    """32-bit fields inside the kernels (chunk bytes, tile count) are guarded by the host: geometry beyond them is
+    refused with KVDP_ERANGE before anything is launched (the buffers here are far smaller than the geometry claims)."""
+    buf, ids = DevBuf(gpu, 1 << 20), DevBuf(gpu, 4096 * 4)
+    ptr = np.array([buf.ptr], dtype=np.uint64)
+
+    def desc(run_bytes):
+        d = gpu.PlanDesc()
+        d.num_layers, d.row_groups, d.prefix_dim, d.rows = 1, 1, 1, 1
+        d.run_bytes = run_bytes
+        d.src_block_stride = d.dst_block_stride = d.dst_row_stride = run_bytes
+        d.src_layer_ptrs, d.dst_layer_ptrs, d.device = ptr.ctypes.data, ptr.ctypes.data, -1
+        return d
+    h = C.c_void_p()
+    assert gpu.lib().kvdp_plan_create(C.byref(h), C.byref(desc(1 << 32))) == gpu.KVDP_ERANGE      # chunk >= 4 GiB
+    assert "4 GiB" in gpu.last_error()
+    gpu.check(gpu.lib().kvdp_plan_create(C.byref(h), C.byref(desc(1 << 31))))                    # 2 GiB chunks: fine
+    gpu.set_option("copy_path", 1)
+    gpu.set_option("tile_bytes", 1024)                       # 2^21 tiles per chunk
+    rc = gpu.lib().kvdp_plan_launch(h, ids.ptr, ids.ptr, 1024, 0, 1, None)                       # x 1024 pairs = 2^31
+    assert rc == gpu.KVDP_ERANGE and "tiles in one launch" in gpu.last_error()
+    assert gpu.lib().kvdp_plan_launch(h, ids.ptr, ids.ptr, 0, 0, 1, None) == 0                   # nothing to do
+    gpu.lib().kvdp_plan_destroy(h)
