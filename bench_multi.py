@@ -231,11 +231,46 @@ def run_multi(args, rank, local_rank, world):
             t = torch.tensor([a.elapsed_time(b) / 1e3], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             return float(t.item())
+        def token_verify(mode, samples=6):
+            """The runner announces sampled (src slot, dst slot, layer, kv); prefill ships the source row over NCCL;
+            decode compares it with what the transfer left in its cache."""
+            runner = is_prefill if mode == "push" else not is_prefill
+            okf = torch.ones(1, dtype=torch.int32, device="cuda")
+            meta = torch.zeros(samples * 4, dtype=torch.int64, device="cuda")
+            if runner:
+                pick = np.random.Generator(np.random.PCG64(5)).integers(0, ntok, size=samples)
+                rows_ = []
+                for j, i in enumerate(pick):
+                    rows_ += [int(ts_ids[i]), int(td_ids[i]), (7 * j) % L8B, j % 2]
+                meta = torch.tensor(rows_, dtype=torch.int64, device="cuda")
+                dist.send(meta, partner)
+            else:
+                dist.recv(meta, partner)
+            rows_ = meta.tolist()
+            for j in range(samples):
+                ss, dd, l, kv = rows_[4 * j:4 * j + 4]
+                if is_prefill:
+                    layer = torch.as_tensor(CudaArray(own_layers[l].value, layer_bytes), device="cuda")
+                    dist.send(layer[(kv * slots + ss) * row:(kv * slots + ss + 1) * row].contiguous(), partner)
+                else:
+                    buf = torch.empty(row, dtype=torch.uint8, device="cuda")
+                    dist.recv(buf, partner)
+                    cache = torch.as_tensor(CudaArray(own_cache.value, n * BLOCK_BYTES), device="cuda")
+                    off = l * layer_bytes + (kv * slots + dd) * row
+                    if not torch.equal(buf, cache[off:off + row]):
+                        okf.zero_()
+            dist.all_reduce(okf, op=dist.ReduceOp.MIN)
+            if int(okf.item()) != 1:
+                raise RuntimeError("token-granular %s result differs from its source" % mode)
+
         token = {"tokens_per_launch": ntok, "run_bytes": row, "runs_per_launch": ntok * 2 * L8B}
         k_t = max(2, min(steps, 10))
         for mode in modes:
+            if not is_prefill:
+                lib.check(L.kvdp_memset(own_cache, 0, n * BLOCK_BYTES))
             token_timed(mode, 2)
             sec_t = token_timed(mode, k_t)
+            token_verify(mode)
             per_dir = ntok * row * 2 * L8B * k_t / sec_t / GB * max(1, P // D)
             token[mode] = {"per_direction_GBps": per_dir, "frac_of_nominal_900": per_dir / NVLINK_PEAK_NOMINAL,
                            "tokens_per_s": P * ntok * k_t / sec_t}
