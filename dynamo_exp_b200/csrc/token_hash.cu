@@ -375,24 +375,42 @@ __global__ void __launch_bounds__(256) kvdp_hash_blocks_parts(const __grid_const
   int64_t r = boff_upper_request(A.block_offsets, A.n_req, w_begin + sub);
   for (int64_t base = w_begin; base < w_end; base += STEP) {
     uint64_t lo[kPartsUnroll], hi[kPartsUnroll];
+    const int64_t g0 = base + sub, g_last = g0 + (kPartsUnroll - 1) * RPI;
+    // request of this lane's first block in the trip (usually unchanged from the last trip)
+    if (g0 < w_end)
+      while (r + 1 < A.n_req && __ldg(A.block_offsets + r + 1) <= g0) ++r;
+    const int64_t r_b0 = __ldg(A.block_offsets + r), r_b1 = __ldg(A.block_offsets + r + 1);
+    const uint32_t* p0 = A.tokens + __ldg(A.offsets + r) + (g0 - r_b0) * (int64_t)A.block_size + 4 * part;
+    if (g_last < w_end && g_last < r_b1 && (reinterpret_cast<uintptr_t>(p0) & 15) == 0) {
+      // the whole trip lies inside one request: constant-stride loads, nothing to look up per block
+      const size_t stride = (size_t)RPI * (size_t)A.block_size;
 #pragma unroll
-    for (int u = 0; u < kPartsUnroll; ++u) {
-      const int64_t gb = base + u * RPI + sub;
-      lo[u] = hi[u] = 0;
-      if (gb < w_end) {
-        // (keeping the request's bounds in registers behind a branch measured 18 % slower than these cached loads)
-        while (r + 1 < A.n_req && __ldg(A.block_offsets + r + 1) <= gb) ++r;
-        const uint32_t* src = A.tokens + __ldg(A.offsets + r) + (gb - __ldg(A.block_offsets + r)) * (int64_t)A.block_size +
-                              4 * part;
-        if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
-          const int4 v = ld_stream16(src);
-          lo[u] = (uint64_t)(uint32_t)v.x | ((uint64_t)(uint32_t)v.y << 32);
-          hi[u] = (uint64_t)(uint32_t)v.z | ((uint64_t)(uint32_t)v.w << 32);
-        } else {  // the request does not start on a 16-byte boundary
-          lo[u] = (uint64_t)__ldg(src) | ((uint64_t)__ldg(src + 1) << 32);
-          hi[u] = (uint64_t)__ldg(src + 2) | ((uint64_t)__ldg(src + 3) << 32);
+      for (int u = 0; u < kPartsUnroll; ++u) {
+        const int4 v = ld_stream16(p0 + u * stride);
+        lo[u] = (uint64_t)(uint32_t)v.x | ((uint64_t)(uint32_t)v.y << 32);
+        hi[u] = (uint64_t)(uint32_t)v.z | ((uint64_t)(uint32_t)v.w << 32);
+      }
+    } else {
+      int64_t rr = r;
+#pragma unroll
+      for (int u = 0; u < kPartsUnroll; ++u) {
+        const int64_t gb = base + u * RPI + sub;
+        lo[u] = hi[u] = 0;
+        if (gb < w_end) {
+          while (rr + 1 < A.n_req && __ldg(A.block_offsets + rr + 1) <= gb) ++rr;
+          const uint32_t* src = A.tokens + __ldg(A.offsets + rr) +
+                                (gb - __ldg(A.block_offsets + rr)) * (int64_t)A.block_size + 4 * part;
+          if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+            const int4 v = ld_stream16(src);
+            lo[u] = (uint64_t)(uint32_t)v.x | ((uint64_t)(uint32_t)v.y << 32);
+            hi[u] = (uint64_t)(uint32_t)v.z | ((uint64_t)(uint32_t)v.w << 32);
+          } else {  // the request does not start on a 16-byte boundary
+            lo[u] = (uint64_t)__ldg(src) | ((uint64_t)__ldg(src + 1) << 32);
+            hi[u] = (uint64_t)__ldg(src + 2) | ((uint64_t)__ldg(src + 3) << 32);
+          }
         }
       }
+      r = rr;
     }
 #pragma unroll
     for (int u = 0; u < kPartsUnroll; ++u) {
