@@ -48,6 +48,10 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--requests", type=int, default=8, help="requests (of 64 blocks) per step")
     ap.add_argument("--cache-blocks", type=int, default=1024, help="blocks in the source / destination caches")
+    ap.add_argument("--pairing", choices=["split", "interleaved"], default="interleaved",
+                    help="N>1: which GPUs prefill: the even ones, each pushing to its odd neighbour (default: GPUs that\n"
+                         "share a PCIe switch are then not both reading host memory in the e2e leg), or the first half")
+    ap.add_argument("--cpu-affinity", type=int, default=0, help="N>1: 1 = bind each rank to the CPUs NVML names for its GPU")
     ap.add_argument("--copy-path", type=int, default=0)
     ap.add_argument("--tile-bytes", type=int, default=0)
     ap.add_argument("--stages", type=int, default=0)

@@ -37,7 +37,14 @@ def run_multi(args, rank, local_rank, world):
     from dynamo_exp_b200 import _lib as lib
     L = lib.lib()
     from dynamo_exp_b200.connector import split_roles
-    prefill_ranks, decode_ranks, role_pairs = split_roles(world)
+    prefill_ranks, decode_ranks, role_pairs = split_roles(world, interleaved=args.pairing == "interleaved")
+    if args.cpu_affinity:
+        try:                                  # run (and first-touch pinned memory) on the CPUs next to this GPU
+            import pynvml
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
+        except Exception:
+            pass
     P, D = len(prefill_ranks), len(decode_ranks)
     is_prefill = rank in prefill_ranks
     partner = dict(role_pairs)[rank] if is_prefill else [p for p, d in role_pairs if d == rank][0]
@@ -334,7 +341,8 @@ def run_multi(args, rank, local_rank, world):
         best = max(results, key=lambda m: results[m]["value"])
         r = results[best]
         cfg = workload_config(args)
-        cfg["pairs"] = ["%d->%d" % (q, P + q % D) for q in range(P)]
+        cfg["pairs"] = ["%d->%d" % (a, b) for a, b in role_pairs]
+        cfg["pairing"] = args.pairing
         cfg["mode"] = best
         line = {
             "metric": "kv_transfer_GBps", "value": r["value"], "unit": "GB/s", "n_gpus": world, "steps": steps,

@@ -248,12 +248,16 @@ def rearrange_tensors(t1_ptr: int, t2_ptr: int, shape: Sequence[int], element_si
             eng.close()
 
 
-def split_roles(world: int):
-    """Prefill:decode split used by the multi-GPU bench (north star: 2/4/8-GPU prefill:decode splits): the first
-    world // 2 ranks prefill, the rest decode; returns (prefill_ranks, decode_ranks, pairs) with prefill rank r paired
-    with decode rank P + r % D."""
+def split_roles(world: int, interleaved: bool = False):
+    """Prefill:decode split used by the multi-GPU bench (north star: 2/4/8-GPU prefill:decode splits). Default: the
+    first world // 2 ranks prefill, the rest decode, prefill rank r paired with decode rank P + r % D. `interleaved`
+    (even world only): even ranks prefill and push to the next odd rank, so that neighbouring GPUs, which usually hang
+    off the same PCIe switch, are not both reading host memory. Returns (prefill_ranks, decode_ranks, pairs)."""
     if world < 2:
         raise KvError("a prefill:decode split needs at least 2 ranks")
+    if interleaved and world % 2 == 0:
+        prefill, decode = list(range(0, world, 2)), list(range(1, world, 2))
+        return prefill, decode, [(r, r + 1) for r in prefill]
     p = world // 2
     d = world - p
     prefill, decode = list(range(p)), list(range(p, world))

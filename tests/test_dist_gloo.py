@@ -82,6 +82,8 @@ def test_split_roles():
     assert split_roles(2) == ([0], [1], [(0, 1)])
     assert split_roles(4) == ([0, 1], [2, 3], [(0, 2), (1, 3)])
     assert split_roles(8)[2] == [(0, 4), (1, 5), (2, 6), (3, 7)]
+    assert split_roles(8, interleaved=True) == ([0, 2, 4, 6], [1, 3, 5, 7], [(0, 1), (2, 3), (4, 5), (6, 7)])
+    assert split_roles(3, interleaved=True) == split_roles(3)           # odd worlds keep the plain split
     p, d, pairs = split_roles(6)
     assert (p, d) == ([0, 1, 2], [3, 4, 5])
 
