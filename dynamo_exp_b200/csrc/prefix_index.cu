@@ -145,6 +145,10 @@ struct kvdp_index {
   cudaStream_t stream = nullptr;
   bool full_upload_needed = true;
   std::recursive_mutex mu;  // events may arrive from the publisher thread while another thread scores requests
+  // host-form lookups: one pinned + one device staging buffer, grown on demand
+  char* h_io = nullptr;
+  char* d_io = nullptr;
+  size_t io_cap = 0;
 };
 
 namespace {
@@ -272,6 +276,8 @@ int kvdp_index_destroy(kvdp_index* ix) {
   if (ix->d_edges) cudaFree(ix->d_edges);
   if (ix->d_idx) cudaFree(ix->d_idx);
   if (ix->d_recs) cudaFree(ix->d_recs);
+  if (ix->d_io) cudaFree(ix->d_io);
+  if (ix->h_io) cudaFreeHost(ix->h_io);
   delete ix;
   return 0;
 }
@@ -414,6 +420,104 @@ int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int6
       ix->d_edges, ix->capacity - 1, ix->nodes[0].gen, d_hashes, d_seq_offsets, n_req, early_exit, num_workers, d_scores,
       d_matched_depth);
   KVDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Host-buffer form: hashes, offsets in; scores (and depths) out; synchronises. One pinned staging buffer, ONE upload and
+// ONE download per call instead of a copy per array, so a single-request lookup costs little more than the launch.
+int kvdp_index_find_matches_host(kvdp_index* ix, const uint64_t* h_hashes, const int64_t* h_seq_offsets, int64_t n_req,
+                                 int32_t early_exit, int32_t num_workers, uint32_t* h_scores, int32_t* h_matched_depth) {
+  if (!ix) return fail(KVDP_EINVAL, "kvdp_index_find_matches_host: NULL handle");
+  if (n_req < 0) return fail(KVDP_EINVAL, "prefix index: negative n_req");
+  if (num_workers < 1 || num_workers > ix->max_workers) return fail(KVDP_EINVAL, "prefix index: num_workers out of range");
+  if (n_req == 0) return 0;
+  if (!h_seq_offsets || !h_scores) return fail(KVDP_EINVAL, "prefix index: NULL pointer");
+  const int64_t n_hash = h_seq_offsets[n_req] - h_seq_offsets[0];
+  if (h_seq_offsets[0] != 0 || n_hash < 0 || (n_hash > 0 && !h_hashes))
+    return fail(KVDP_EINVAL, "prefix index: offsets must start at 0 and hashes must be given");
+  std::lock_guard<std::recursive_mutex> guard(ix->mu);
+  DeviceGuard g(ix->device);
+  const size_t in_hash = (size_t)n_hash * 8, in_off = (size_t)(n_req + 1) * 8;
+  const size_t out_scores = (size_t)n_req * num_workers * 4, out_depth = (size_t)n_req * 4;
+  const size_t in_bytes = (in_hash + in_off + 15) & ~(size_t)15;
+  const size_t need = in_bytes + out_scores + out_depth;
+  if (need > ix->io_cap) {
+    KVDP_CUDA(cudaStreamSynchronize(ix->stream));
+    if (ix->d_io) cudaFree(ix->d_io);
+    if (ix->h_io) cudaFreeHost(ix->h_io);
+    ix->d_io = ix->h_io = nullptr;
+    ix->io_cap = 0;
+    const size_t cap = std::max<size_t>(need * 2, 1 << 16);
+    KVDP_CUDA(cudaMalloc((void**)&ix->d_io, cap));
+    KVDP_CUDA(cudaHostAlloc((void**)&ix->h_io, cap, cudaHostAllocDefault));
+    ix->io_cap = cap;
+  }
+  memcpy(ix->h_io, h_seq_offsets, in_off);          // offsets first: 8-byte aligned either way
+  if (in_hash) memcpy(ix->h_io + in_off, h_hashes, in_hash);
+  KVDP_CUDA(cudaMemcpyAsync(ix->d_io, ix->h_io, in_off + in_hash, cudaMemcpyHostToDevice, ix->stream));
+  uint32_t* d_scores = (uint32_t*)(ix->d_io + in_bytes);
+  int32_t* d_depth = (int32_t*)(ix->d_io + in_bytes + out_scores);
+  if (int rc = kvdp_index_find_matches(ix, (const uint64_t*)(ix->d_io + in_off), (const int64_t*)ix->d_io, n_req,
+                                       early_exit, num_workers, d_scores, d_depth, nullptr))
+    return rc;
+  KVDP_CUDA(cudaMemcpyAsync(ix->h_io + in_bytes, d_scores, out_scores + out_depth, cudaMemcpyDeviceToHost, ix->stream));
+  KVDP_CUDA(cudaStreamSynchronize(ix->stream));
+  memcpy(h_scores, ix->h_io + in_bytes, out_scores);
+  if (h_matched_depth) memcpy(h_matched_depth, ix->h_io + in_bytes + out_scores, out_depth);
+  return 0;
+}
+
+// KvIndexer::find_matches_for_request (indexer.rs:639-651) for a batch of token sequences held by the host: hash the full
+// blocks (seed 1337, un-chained) and walk the tree in the same round trip — one upload, scan + hash + find kernels on
+// the index's stream, one download.
+int kvdp_index_find_matches_for_tokens_host(kvdp_index* ix, const uint32_t* h_tokens, const int64_t* h_offsets,
+                                            int64_t n_req, int32_t block_size, int32_t early_exit, int32_t num_workers,
+                                            uint32_t* h_scores, int32_t* h_matched_depth) {
+  if (!ix) return fail(KVDP_EINVAL, "kvdp_index_find_matches_for_tokens_host: NULL handle");
+  if (n_req < 0 || block_size < 1) return fail(KVDP_EINVAL, "prefix index: bad n_req / block_size");
+  if (num_workers < 1 || num_workers > ix->max_workers) return fail(KVDP_EINVAL, "prefix index: num_workers out of range");
+  if (n_req == 0) return 0;
+  if (!h_offsets || !h_scores) return fail(KVDP_EINVAL, "prefix index: NULL pointer");
+  const int64_t total = h_offsets[n_req];
+  if (h_offsets[0] != 0 || total < 0 || (total > 0 && !h_tokens))
+    return fail(KVDP_EINVAL, "prefix index: offsets must start at 0 and tokens must be given");
+  std::lock_guard<std::recursive_mutex> guard(ix->mu);
+  DeviceGuard g(ix->device);
+  auto up16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
+  const size_t b_off = (size_t)(n_req + 1) * 8, b_tok = up16((size_t)total * 4);
+  const int64_t max_blocks = total / block_size;
+  const size_t b_bh = up16((size_t)std::max<int64_t>(max_blocks, 1) * 8), b_ws = up16(kvdp_hash_workspace_bytes(n_req));
+  const size_t out_scores = (size_t)n_req * num_workers * 4, out_depth = (size_t)n_req * 4;
+  const size_t o_tok = up16(b_off), o_boff = o_tok + b_tok, o_bh = o_boff + up16(b_off), o_ws = o_bh + b_bh;
+  const size_t o_out = (o_ws + b_ws + 255) & ~(size_t)255;
+  const size_t need = o_out + out_scores + out_depth;
+  if (need > ix->io_cap) {
+    KVDP_CUDA(cudaStreamSynchronize(ix->stream));
+    if (ix->d_io) cudaFree(ix->d_io);
+    if (ix->h_io) cudaFreeHost(ix->h_io);
+    ix->d_io = ix->h_io = nullptr;
+    ix->io_cap = 0;
+    const size_t cap = std::max<size_t>(need * 2, 1 << 16);
+    KVDP_CUDA(cudaMalloc((void**)&ix->d_io, cap));
+    KVDP_CUDA(cudaHostAlloc((void**)&ix->h_io, cap, cudaHostAllocDefault));
+    ix->io_cap = cap;
+  }
+  memcpy(ix->h_io, h_offsets, b_off);
+  if (total) memcpy(ix->h_io + o_tok, h_tokens, (size_t)total * 4);
+  KVDP_CUDA(cudaMemcpyAsync(ix->d_io, ix->h_io, o_tok + (size_t)total * 4, cudaMemcpyHostToDevice, ix->stream));
+  int64_t* d_boff = (int64_t*)(ix->d_io + o_boff);
+  uint64_t* d_bh = (uint64_t*)(ix->d_io + o_bh);
+  if (int rc = kvdp_hash_token_blocks((const uint32_t*)(ix->d_io + o_tok), (const int64_t*)ix->d_io, n_req, total, block_size,
+                                      1337, d_boff, d_bh, nullptr, ix->d_io + o_ws, b_ws, 0, (kvdp_stream_t)ix->stream))
+    return rc;
+  uint32_t* d_scores = (uint32_t*)(ix->d_io + o_out);
+  int32_t* d_depth = (int32_t*)(ix->d_io + o_out + out_scores);
+  if (int rc = kvdp_index_find_matches(ix, d_bh, d_boff, n_req, early_exit, num_workers, d_scores, d_depth, nullptr))
+    return rc;
+  KVDP_CUDA(cudaMemcpyAsync(ix->h_io + o_out, d_scores, out_scores + out_depth, cudaMemcpyDeviceToHost, ix->stream));
+  KVDP_CUDA(cudaStreamSynchronize(ix->stream));
+  memcpy(h_scores, ix->h_io + o_out, out_scores);
+  if (h_matched_depth) memcpy(h_matched_depth, ix->h_io + o_out + out_scores, out_depth);
   return 0;
 }
 

@@ -183,36 +183,28 @@ class RadixTree:
             return np.zeros((0, nw), dtype=np.uint32), np.zeros(0, dtype=np.int32)
         hashes = np.ascontiguousarray(hashes, dtype=np.uint64)
         seq_offsets = np.ascontiguousarray(seq_offsets, dtype=np.int64)
-        sizes = [max(hashes.nbytes, 8), seq_offsets.nbytes, n_req * nw * 4, n_req * 4]
-        bufs = self._scratch(sizes)
-        _lib.check(L.cuda_memcpy_sync(bufs[0], hashes.ctypes.data, hashes.nbytes))
-        _lib.check(L.cuda_memcpy_sync(bufs[1], seq_offsets.ctypes.data, seq_offsets.nbytes))
-        _lib.check(L.kvdp_index_find_matches(self._h, bufs[0], bufs[1], n_req, int(early_exit), nw, bufs[2], bufs[3],
-                                             None))
-        stream = L.kvdp_index_stream(self._h)
         scores = np.zeros((n_req, nw), dtype=np.uint32)
         depth = np.zeros(n_req, dtype=np.int32)
-        _lib.check(L.cuda_memcpy_async(scores.ctypes.data, bufs[2], scores.nbytes, stream))
-        _lib.check(L.cuda_memcpy_async(depth.ctypes.data, bufs[3], depth.nbytes, stream))
-        _lib.check(L.kvdp_stream_synchronize(stream))
+        _lib.check(L.kvdp_index_find_matches_host(self._h, hashes.ctypes.data if hashes.size else None,
+                                                  seq_offsets.ctypes.data, n_req, int(early_exit), nw,
+                                                  scores.ctypes.data, depth.ctypes.data))
         return scores, depth
 
-    def _scratch(self, sizes):
-        """Device buffers for a lookup, kept between calls and grown when a batch needs more (a lookup per request must
-        not pay four allocations)."""
-        L = _lib.lib()
-        if not hasattr(self, "_bufs"):
-            self._bufs = [[C.c_void_p(), 0] for _ in sizes]
-        for slot, need in zip(self._bufs, sizes):
-            if slot[1] < need:
-                if slot[0].value:
-                    _lib.check(L.kvdp_stream_synchronize(L.kvdp_index_stream(self._h)))
-                    L.kvdp_device_free(slot[0])
-                    slot[0], slot[1] = C.c_void_p(), 0
-                cap = max(int(need), 2 * slot[1], 4096)
-                _lib.check(L.kvdp_device_alloc(C.byref(slot[0]), cap, self._device))
-                slot[1] = cap
-        return [slot[0] for slot in self._bufs]
+    def scores_for_tokens(self, requests: Sequence, kv_block_size: int) -> np.ndarray:
+        """[n_req][workers in use] overlap counts for token sequences: seed-1337 block hashing and the tree walk happen
+        in one upload / launch sequence / download."""
+        toks = [_as_u32(t) for t in requests]
+        n_req = len(toks)
+        nw = max(max([s for s in self._slot.values()], default=-1) + 1, 1)
+        if n_req == 0:
+            return np.zeros((0, nw), dtype=np.uint32)
+        offs = np.zeros(n_req + 1, dtype=np.int64)
+        offs[1:] = np.cumsum([t.size for t in toks])
+        flat = np.ascontiguousarray(np.concatenate(toks)) if offs[-1] else np.zeros(1, dtype=np.uint32)
+        scores = np.zeros((n_req, nw), dtype=np.uint32)
+        _lib.check(_lib.lib().kvdp_index_find_matches_for_tokens_host(
+            self._h, flat.ctypes.data, offs.ctypes.data, n_req, int(kv_block_size), 0, nw, scores.ctypes.data, None))
+        return scores
 
     def _to_overlap(self, row: np.ndarray) -> OverlapScores:
         out = OverlapScores()
@@ -230,10 +222,6 @@ class RadixTree:
 
     def close(self) -> None:
         if self._h is not None and self._h.value:
-            for slot in getattr(self, "_bufs", []):
-                if slot[0].value:
-                    _lib.lib().kvdp_device_free(slot[0])
-            self._bufs = []
             _lib.lib().kvdp_index_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -268,14 +256,9 @@ class KvIndexer:
         return self.find_matches_for_requests([tokens])[0]
 
     def find_matches_for_requests(self, requests: Sequence) -> List[OverlapScores]:
-        """Batched form: token lists in, one OverlapScores per request out; hashing and matching both on the GPU."""
-        from .tokens import hash_token_blocks
-        toks = [_as_u32(t) for t in requests]
-        offs = np.zeros(len(toks) + 1, dtype=np.int64)
-        offs[1:] = np.cumsum([t.size for t in toks])
-        flat = np.concatenate(toks) if toks else np.zeros(0, dtype=np.uint32)
-        boff, bh, _ = hash_token_blocks(flat, offs, self.kv_block_size, XXH3_SEED, chained=False)
-        scores, _ = self.tree.find_matches_device_arrays(bh if bh.size else np.zeros(1, dtype=np.uint64), boff, False)
+        """Batched form: token lists in, one OverlapScores per request out; hashing and matching in ONE round trip to the
+        GPU (kvdp_index_find_matches_for_tokens_host)."""
+        scores = self.tree.scores_for_tokens(requests, self.kv_block_size)
         return [self.tree._to_overlap(row) for row in scores]
 
 
@@ -334,16 +317,9 @@ class KvIndexerSharded:
         return self.find_matches_for_requests([tokens])[0]
 
     def find_matches_for_requests(self, requests: Sequence) -> List[OverlapScores]:
-        from .tokens import hash_token_blocks
-        toks = [_as_u32(t) for t in requests]
-        offs = np.zeros(len(toks) + 1, dtype=np.int64)
-        offs[1:] = np.cumsum([t.size for t in toks])
-        flat = np.concatenate(toks) if toks else np.zeros(0, dtype=np.uint32)
-        boff, bh, _ = hash_token_blocks(flat, offs, self.kv_block_size, XXH3_SEED, chained=False)
-        hashes = bh if bh.size else np.zeros(1, dtype=np.uint64)
-        per_shard = [[t._to_overlap(row) for row in t.find_matches_device_arrays(hashes, boff, False)[0]]
+        per_shard = [[t._to_overlap(row) for row in t.scores_for_tokens(requests, self.kv_block_size)]
                      for t in self.shards]
-        return [self._merge([ps[i] for ps in per_shard]) for i in range(len(toks))]
+        return [self._merge([ps[i] for ps in per_shard]) for i in range(len(requests))]
 
     def shutdown(self) -> None:
         for t in self.shards:

@@ -288,6 +288,15 @@ int kvdp_index_flush(kvdp_index* ix);
 int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int64_t* d_seq_offsets, int64_t n_req,
                             int32_t early_exit, int32_t num_workers, uint32_t* d_scores, int32_t* d_matched_depth,
                             kvdp_stream_t stream);
+/* The same lookup for host arrays (what a router thread holds): one upload, one launch, one download, synchronous.
+ * h_seq_offsets[0] must be 0; h_scores is [n_req][num_workers], h_matched_depth[n_req] may be NULL. */
+int kvdp_index_find_matches_host(kvdp_index* ix, const uint64_t* h_hashes, const int64_t* h_seq_offsets, int64_t n_req,
+                                 int32_t early_exit, int32_t num_workers, uint32_t* h_scores, int32_t* h_matched_depth);
+/* KvIndexer::find_matches_for_request (indexer.rs:639-651) for a batch: token sequences in (CSR, h_offsets[0] == 0), the
+ * full blocks are hashed with seed 1337 and matched in the same round trip. Outputs as above. */
+int kvdp_index_find_matches_for_tokens_host(kvdp_index* ix, const uint32_t* h_tokens, const int64_t* h_offsets,
+                                            int64_t n_req, int32_t block_size, int32_t early_exit, int32_t num_workers,
+                                            uint32_t* h_scores, int32_t* h_matched_depth);
 /* Introspection for tests: what = 0 nodes; 1 children of node `arg`; 2 lookup entries of worker `arg`; 3 workers on node
  * `arg`; 4 root's child for tokens hash `arg` (node id or -1); 5 workers with a lookup table; 6 nodes whose worker set
  * still holds slot `arg` (0 right after kvdp_index_remove_worker means the slot can serve another worker id). */

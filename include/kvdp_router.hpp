@@ -53,15 +53,11 @@ struct OverlapScores {           // indexer.rs:390-436 (frequencies stay empty: 
 // ------------------------------------------------------------------------------------------------ prefix index
 class RadixTree {  // indexer.rs:187-387
  public:
-  explicit RadixTree(int64_t max_nodes = 1 << 20, int device = -1) : device_(device) {
+  explicit RadixTree(int64_t max_nodes = 1 << 20, int device = -1) {
     if (kvdp_index_create(&ix_, max_nodes, kMaxWorkers, device) != 0) raise(kvdp_last_error());
     slot_worker_.assign(kMaxWorkers, std::nullopt);
   }
-  ~RadixTree() {
-    for (auto& b : scratch_)
-      if (b.ptr) kvdp_device_free(b.ptr);
-    kvdp_index_destroy(ix_);
-  }
+  ~RadixTree() { kvdp_index_destroy(ix_); }
   RadixTree(const RadixTree&) = delete;
   RadixTree& operator=(const RadixTree&) = delete;
 
@@ -105,21 +101,29 @@ class RadixTree {  // indexer.rs:187-387
     for (int64_t i = 0; i < n; ++i) offs[i + 1] = offs[i] + (int64_t)sequences[i].size();
     std::vector<uint64_t> flat((size_t)std::max<int64_t>(offs[n], 1), 0);
     for (int64_t i = 0; i < n; ++i) std::copy(sequences[i].begin(), sequences[i].end(), flat.begin() + offs[i]);
-    int nw = 1;
-    for (size_t s = 0; s < slot_worker_.size(); ++s)
-      if (slot_worker_[s]) nw = (int)s + 1;
-    const size_t need[4] = {flat.size() * 8, offs.size() * 8, (size_t)n * nw * 4, (size_t)n * 4};
-    for (int k = 0; k < 4; ++k) reserve(k, need[k]);
+    const int nw = workers_in_use();
     std::vector<uint32_t> scores((size_t)n * nw);
-    kvdp_stream_t st = kvdp_index_stream(ix_);
-    int rc = cuda_memcpy_sync(scratch_[0].ptr, flat.data(), need[0]);
-    if (!rc) rc = cuda_memcpy_sync(scratch_[1].ptr, offs.data(), need[1]);
-    if (!rc)
-      rc = kvdp_index_find_matches(ix_, (const uint64_t*)scratch_[0].ptr, (const int64_t*)scratch_[1].ptr, n,
-                                   early_exit ? 1 : 0, nw, (uint32_t*)scratch_[2].ptr, (int32_t*)scratch_[3].ptr, nullptr);
-    if (!rc) rc = cuda_memcpy_async(scores.data(), scratch_[2].ptr, need[2], st);
-    if (!rc) rc = kvdp_stream_synchronize(st);
-    if (rc) raise(kvdp_last_error());
+    if (kvdp_index_find_matches_host(ix_, flat.data(), offs.data(), n, early_exit ? 1 : 0, nw, scores.data(), nullptr) != 0)
+      raise(kvdp_last_error());
+    for (int64_t i = 0; i < n; ++i)
+      for (int s = 0; s < nw; ++s)
+        if (scores[(size_t)i * nw + s] && slot_worker_[s]) out[i].scores[*slot_worker_[s]] = scores[(size_t)i * nw + s];
+    return out;
+  }
+  // Token sequences in: seed-1337 block hashing and the walk in one round trip to the GPU (new).
+  std::vector<OverlapScores> find_matches_for_tokens(const std::vector<std::vector<Token>>& requests, size_t block_size) {
+    const int64_t n = (int64_t)requests.size();
+    std::vector<OverlapScores> out((size_t)n);
+    if (n == 0) return out;
+    std::vector<int64_t> offs((size_t)n + 1, 0);
+    for (int64_t i = 0; i < n; ++i) offs[i + 1] = offs[i] + (int64_t)requests[i].size();
+    std::vector<Token> flat((size_t)std::max<int64_t>(offs[n], 1), 0);
+    for (int64_t i = 0; i < n; ++i) std::copy(requests[i].begin(), requests[i].end(), flat.begin() + offs[i]);
+    const int nw = workers_in_use();
+    std::vector<uint32_t> scores((size_t)n * nw);
+    if (kvdp_index_find_matches_for_tokens_host(ix_, flat.data(), offs.data(), n, (int32_t)block_size, 0, nw, scores.data(),
+                                                nullptr) != 0)
+      raise(kvdp_last_error());
     for (int64_t i = 0; i < n; ++i)
       for (int s = 0; s < nw; ++s)
         if (scores[(size_t)i * nw + s] && slot_worker_[s]) out[i].scores[*slot_worker_[s]] = scores[(size_t)i * nw + s];
@@ -143,27 +147,15 @@ class RadixTree {  // indexer.rs:187-387
 
  private:
   static constexpr int kMaxWorkers = 64;
-  struct Buf {
-    void* ptr = nullptr;
-    size_t cap = 0;
-  };
-  void reserve(int k, size_t need) {
-    Buf& b = scratch_[k];
-    if (b.cap >= need) return;
-    if (b.ptr) {
-      kvdp_stream_synchronize(kvdp_index_stream(ix_));
-      kvdp_device_free(b.ptr);
-      b = Buf{};
-    }
-    const size_t cap = std::max<size_t>({need, 2 * b.cap, 4096});
-    if (kvdp_device_alloc(&b.ptr, cap, device_) != 0) raise(kvdp_last_error());
-    b.cap = cap;
+  int workers_in_use() const {  // highest bound slot + 1 (at least 1): the width of the score rows
+    int nw = 1;
+    for (size_t s = 0; s < slot_worker_.size(); ++s)
+      if (slot_worker_[s]) nw = (int)s + 1;
+    return nw;
   }
   kvdp_index* ix_ = nullptr;
-  int device_;
   std::unordered_map<WorkerId, int> worker_slot_;
   std::vector<std::optional<WorkerId>> slot_worker_;
-  Buf scratch_[4];
 };
 
 class KvIndexer {  // indexer.rs:498-667, without the actor
@@ -175,7 +167,7 @@ class KvIndexer {  // indexer.rs:498-667, without the actor
   void remove_worker(WorkerId w) { tree_.remove_worker(w); }
   OverlapScores find_matches(const std::vector<uint64_t>& sequence) { return tree_.find_matches(sequence, false); }
   OverlapScores find_matches_for_request(const std::vector<Token>& tokens) {  // indexer.rs:639-651
-    return tree_.find_matches(compute_block_hash_for_seq(tokens, kv_block_size_), false);
+    return tree_.find_matches_for_tokens({tokens}, kv_block_size_)[0];
   }
   RadixTree& tree() { return tree_; }
 
@@ -220,7 +212,10 @@ class KvIndexerSharded {  // indexer.rs:677-884: a worker goes to the shard that
     return out;
   }
   OverlapScores find_matches_for_request(const std::vector<Token>& tokens) {
-    return find_matches(compute_block_hash_for_seq(tokens, kv_block_size_));
+    OverlapScores out;
+    for (auto& s : shards_)
+      for (auto& kv : s->find_matches_for_tokens({tokens}, kv_block_size_)[0].scores) out.scores[kv.first] = kv.second;
+    return out;
   }
   const std::vector<size_t>& worker_counts() const { return counts_; }
 
