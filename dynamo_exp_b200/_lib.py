@@ -126,6 +126,7 @@ PROTOTYPES = {
     "kvdp_index_find_matches": (_i, [_vp, _vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp]),
     "kvdp_index_find_matches_host": (_i, [_vp, _vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     "kvdp_index_find_matches_for_tokens_host": (_i, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp, _vp]),
+    "kvdp_index_touch": (_i64, [_vp, _vp, _i64, _i32, _i64, _i64, _vp, _i64]),
     "kvdp_index_stat": (_i64, [_vp, _i32, _u64]),
     # §I engine-facing KV-event ABI (argtypes as in the reference's CtypesEventPublisher fixture,
     # lib/bindings/python/tests/test_kv_bindings.py:141-176)

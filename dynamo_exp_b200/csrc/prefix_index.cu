@@ -20,6 +20,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <deque>
 #include <mutex>
 #include <unordered_map>
 #include <vector>
@@ -117,6 +118,7 @@ struct HostNode {
   std::vector<uint32_t> in_slots;                    // edge-table slots of edges that point at this node
   uint64_t workers = 0;
   uint32_t gen = 0;
+  std::deque<int64_t> recent_uses;  // access times (ns) inside the expiration window; only kept when tracking is on
 };
 
 }  // namespace
@@ -519,6 +521,33 @@ int kvdp_index_find_matches_for_tokens_host(kvdp_index* ix, const uint32_t* h_to
   memcpy(h_scores, ix->h_io + o_out, out_scores);
   if (h_matched_depth) memcpy(h_matched_depth, ix->h_io + o_out + out_scores, out_depth);
   return 0;
+}
+
+// Access-frequency bookkeeping of RadixTree::find_matches when the tree was built with an expiration duration
+// (indexer.rs:217-223, 251-267): every block on the matched path keeps the times it was visited; a visit first drops
+// the entries older than `expiration_ns`, reports how many are left (zeros are not reported, :429-436) and then records
+// itself. This is per-request, order-dependent host state, so it lives with the host tree; the scores still come from
+// the GPU walk. Returns the number of frequencies written (they are non-increasing along the path), or a negative
+// KVDP_E* code; `cap` must hold one entry per block of the sequence.
+int64_t kvdp_index_touch(kvdp_index* ix, const uint64_t* h_hashes, int64_t n, int32_t early_exit, int64_t now_ns,
+                         int64_t expiration_ns, uint64_t* h_frequencies, int64_t cap) {
+  if (!ix) return fail(KVDP_EINVAL, "kvdp_index_touch: NULL handle");
+  if (n < 0 || (n > 0 && !h_hashes) || cap < n || (n > 0 && !h_frequencies))
+    return fail(KVDP_EINVAL, "kvdp_index_touch: bad arguments (cap must be >= n)");
+  std::lock_guard<std::recursive_mutex> guard(ix->mu);
+  uint32_t current = 0;
+  int64_t written = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    auto it = ix->nodes[current].children.find(h_hashes[i]);
+    if (it == ix->nodes[current].children.end()) break;
+    HostNode& b = ix->nodes[it->second];
+    while (!b.recent_uses.empty() && now_ns - b.recent_uses.front() > expiration_ns) b.recent_uses.pop_front();
+    if (!b.recent_uses.empty()) h_frequencies[written++] = (uint64_t)b.recent_uses.size();
+    b.recent_uses.push_back(now_ns);
+    if (early_exit && __builtin_popcountll(b.workers) == 1) break;
+    current = it->second;
+  }
+  return written;
 }
 
 // sizes of the host-side structures, for the reference tests' assertions:

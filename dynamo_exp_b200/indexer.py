@@ -106,8 +106,11 @@ class OverlapScores:                     # indexer.rs:390-436
 class RadixTree:
     """reference: indexer.rs:187-387. Events are applied on the host inside libkvdp.so; lookups run on the GPU."""
 
-    def __init__(self, max_nodes: int = 1 << 20, device: int = -1):
+    def __init__(self, max_nodes: int = 1 << 20, device: int = -1, expiration_duration: Optional[float] = None):
+        """`expiration_duration` (seconds) is `RadixTree::new_with_frequency` (indexer.rs:217-223): lookups then also
+        report how often each matched block was visited inside that window."""
         _lib.require_gpu()
+        self.expiration_duration = expiration_duration
         h = C.c_void_p()
         _lib.check(_lib.lib().kvdp_index_create(C.byref(h), int(max_nodes), MAX_WORKERS, int(device)))
         self._h = h
@@ -156,8 +159,21 @@ class RadixTree:
             del self._slot[worker]
             self._worker_of_slot[slot] = None
 
-    def find_matches_batch(self, sequences: Sequence[Sequence[int]], early_exit: bool = False) -> List[OverlapScores]:
-        """Score many requests (each a list of LocalBlockHash) in one launch."""
+    def _frequencies(self, sequence: np.ndarray, early_exit: bool, now: Optional[float]) -> List[int]:
+        import time
+        now_ns = time.monotonic_ns() if now is None else int(round(now * 1e9))
+        out = np.zeros(max(sequence.size, 1), dtype=np.uint64)
+        n = _lib.lib().kvdp_index_touch(self._h, sequence.ctypes.data if sequence.size else None, sequence.size,
+                                        int(early_exit), now_ns, int(round(self.expiration_duration * 1e9)),
+                                        out.ctypes.data, out.size)
+        if n < 0:
+            _lib.check(int(n))
+        return [int(x) for x in out[:n]]
+
+    def find_matches_batch(self, sequences: Sequence[Sequence[int]], early_exit: bool = False,
+                           now: Optional[float] = None) -> List[OverlapScores]:
+        """Score many requests (each a list of LocalBlockHash) in one launch. With an expiration duration the visit
+        bookkeeping runs per request in list order (`now`: clock override in seconds, for tests)."""
         lens = np.array([len(s) for s in sequences], dtype=np.int64)
         offs = np.zeros(len(sequences) + 1, dtype=np.int64)
         offs[1:] = np.cumsum(lens)
@@ -167,11 +183,15 @@ class RadixTree:
             flat[pos:pos + len(s)] = np.asarray(s, dtype=np.uint64)
             pos += len(s)
         scores, _ = self.find_matches_device_arrays(flat, offs, early_exit)
-        return [self._to_overlap(row) for row in scores]
+        out = [self._to_overlap(row) for row in scores]
+        if self.expiration_duration is not None:
+            for i, o in enumerate(out):
+                o.frequencies = self._frequencies(flat[offs[i]:offs[i + 1]], early_exit, now)
+        return out
 
-    def find_matches(self, sequence: Sequence[int], early_exit: bool = False) -> OverlapScores:
+    def find_matches(self, sequence: Sequence[int], early_exit: bool = False, now: Optional[float] = None) -> OverlapScores:
         """reference: indexer.rs:239-277 (one request)."""
-        return self.find_matches_batch([list(sequence)], early_exit)[0]
+        return self.find_matches_batch([list(sequence)], early_exit, now)[0]
 
     def find_matches_device_arrays(self, hashes: np.ndarray, seq_offsets: np.ndarray, early_exit: bool = False):
         """Host arrays in, dense [n_req][MAX_WORKERS-in-use] scores out (slot order) plus matched depths."""
@@ -235,9 +255,15 @@ class RadixTree:
 class KvIndexer:
     """reference: KvIndexer (indexer.rs:498-667) without the tokio actor: same calls, synchronous."""
 
-    def __init__(self, kv_block_size: int, max_nodes: int = 1 << 20, device: int = -1):
+    def __init__(self, kv_block_size: int, max_nodes: int = 1 << 20, device: int = -1,
+                 expiration_duration: Optional[float] = None):
         self.kv_block_size = int(kv_block_size)
-        self.tree = RadixTree(max_nodes, device)
+        self.tree = RadixTree(max_nodes, device, expiration_duration)
+
+    @classmethod
+    def new_with_frequency(cls, expiration_duration: Optional[float], kv_block_size: int, **kw) -> "KvIndexer":
+        """reference: indexer.rs:525-593."""
+        return cls(kv_block_size, expiration_duration=expiration_duration, **kw)
 
     def block_size(self) -> int:
         return self.kv_block_size
@@ -248,8 +274,8 @@ class KvIndexer:
     def remove_worker(self, worker: WorkerId) -> None:
         self.tree.remove_worker(worker)
 
-    def find_matches(self, sequence: Sequence[int]) -> OverlapScores:
-        return self.tree.find_matches(sequence, False)
+    def find_matches(self, sequence: Sequence[int], now: Optional[float] = None) -> OverlapScores:
+        return self.tree.find_matches(sequence, False, now)
 
     def find_matches_for_request(self, tokens) -> OverlapScores:
         """reference: indexer.rs:639-651 — hash the request's full blocks (seed 1337, un-chained), then match."""
@@ -258,6 +284,9 @@ class KvIndexer:
     def find_matches_for_requests(self, requests: Sequence) -> List[OverlapScores]:
         """Batched form: token lists in, one OverlapScores per request out; hashing and matching in ONE round trip to the
         GPU (kvdp_index_find_matches_for_tokens_host)."""
+        if self.tree.expiration_duration is not None:          # the visit bookkeeping needs the block hashes on the host
+            from .tokens import compute_block_hash_for_seq
+            return self.tree.find_matches_batch([compute_block_hash_for_seq(t, self.kv_block_size) for t in requests])
         scores = self.tree.scores_for_tokens(requests, self.kv_block_size)
         return [self.tree._to_overlap(row) for row in scores]
 
@@ -268,11 +297,12 @@ class KvIndexerSharded:
     Here each shard is one device-resident prefix index, which also lifts the 64-worker limit of a single index to
     64 x num_shards. Like the reference, a worker's binding is dropped by remove_worker and chosen afresh afterwards."""
 
-    def __init__(self, num_shards: int, kv_block_size: int, max_nodes: int = 1 << 20, device: int = -1):
+    def __init__(self, num_shards: int, kv_block_size: int, max_nodes: int = 1 << 20, device: int = -1,
+                 expiration_duration: Optional[float] = None):
         if num_shards < 1:
             raise KvError("num_shards must be at least 1")
         self.kv_block_size = int(kv_block_size)
-        self.shards = [RadixTree(max_nodes, device) for _ in range(int(num_shards))]
+        self.shards = [RadixTree(max_nodes, device, expiration_duration) for _ in range(int(num_shards))]
         self.worker_assignments: Dict[WorkerId, int] = {}
         self.worker_counts = [0] * int(num_shards)
 
@@ -306,17 +336,20 @@ class KvIndexerSharded:
                     out.frequencies[i] += f
         return out
 
-    def find_matches_batch(self, sequences: Sequence[Sequence[int]]) -> List[OverlapScores]:
-        per_shard = [t.find_matches_batch(sequences, False) for t in self.shards]
+    def find_matches_batch(self, sequences: Sequence[Sequence[int]], now: Optional[float] = None) -> List[OverlapScores]:
+        per_shard = [t.find_matches_batch(sequences, False, now) for t in self.shards]
         return [self._merge([ps[i] for ps in per_shard]) for i in range(len(sequences))]
 
-    def find_matches(self, sequence: Sequence[int]) -> OverlapScores:
-        return self.find_matches_batch([list(sequence)])[0]
+    def find_matches(self, sequence: Sequence[int], now: Optional[float] = None) -> OverlapScores:
+        return self.find_matches_batch([list(sequence)], now)[0]
 
     def find_matches_for_request(self, tokens) -> OverlapScores:
         return self.find_matches_for_requests([tokens])[0]
 
     def find_matches_for_requests(self, requests: Sequence) -> List[OverlapScores]:
+        if self.shards[0].expiration_duration is not None:
+            from .tokens import compute_block_hash_for_seq
+            return self.find_matches_batch([compute_block_hash_for_seq(t, self.kv_block_size) for t in requests])
         per_shard = [[t._to_overlap(row) for row in t.scores_for_tokens(requests, self.kv_block_size)]
                      for t in self.shards]
         return [self._merge([ps[i] for ps in per_shard]) for i in range(len(requests))]

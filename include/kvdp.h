@@ -297,6 +297,12 @@ int kvdp_index_find_matches_host(kvdp_index* ix, const uint64_t* h_hashes, const
 int kvdp_index_find_matches_for_tokens_host(kvdp_index* ix, const uint32_t* h_tokens, const int64_t* h_offsets,
                                             int64_t n_req, int32_t block_size, int32_t early_exit, int32_t num_workers,
                                             uint32_t* h_scores, int32_t* h_matched_depth);
+/* Access-frequency tracking of a tree built with an expiration duration (indexer.rs:217-223, 251-267): call once per
+ * looked-up sequence, in request order, next to the lookup. Every block on the matched path drops visit times older than
+ * expiration_ns, reports how many remain (zero counts are skipped, like OverlapScores::add_frequency) and records
+ * now_ns. Host-side state. Returns the number of frequencies written to h_frequencies (cap >= n), negative on misuse. */
+int64_t kvdp_index_touch(kvdp_index* ix, const uint64_t* h_hashes, int64_t n, int32_t early_exit, int64_t now_ns,
+                         int64_t expiration_ns, uint64_t* h_frequencies, int64_t cap);
 /* Introspection for tests: what = 0 nodes; 1 children of node `arg`; 2 lookup entries of worker `arg`; 3 workers on node
  * `arg`; 4 root's child for tokens hash `arg` (node id or -1); 5 workers with a lookup table; 6 nodes whose worker set
  * still holds slot `arg` (0 right after kvdp_index_remove_worker means the slot can serve another worker id). */

@@ -11,6 +11,7 @@
 // libkvdp.so (batched entry points are added next to the per-request ones); the pool is plain host logic, as it is there.
 // Header-only; link with -lkvdp.
 #pragma once
+#include <chrono>
 #include <deque>
 #include <functional>
 #include <map>
@@ -45,7 +46,7 @@ struct RouterEvent {             // indexer.rs:139-160
   WorkerId worker_id = 0;
   KvCacheEvent event;
 };
-struct OverlapScores {           // indexer.rs:390-436 (frequencies stay empty: expiration_duration = None)
+struct OverlapScores {           // indexer.rs:390-436 (frequencies: only with an expiration duration)
   std::map<WorkerId, uint32_t> scores;
   std::vector<size_t> frequencies;
 };
@@ -53,7 +54,9 @@ struct OverlapScores {           // indexer.rs:390-436 (frequencies stay empty: 
 // ------------------------------------------------------------------------------------------------ prefix index
 class RadixTree {  // indexer.rs:187-387
  public:
-  explicit RadixTree(int64_t max_nodes = 1 << 20, int device = -1) {
+  // `expiration_s`: RadixTree::new_with_frequency (indexer.rs:217-223); lookups then also report visit frequencies
+  explicit RadixTree(int64_t max_nodes = 1 << 20, int device = -1, std::optional<double> expiration_s = std::nullopt)
+      : expiration_s_(expiration_s) {
     if (kvdp_index_create(&ix_, max_nodes, kMaxWorkers, device) != 0) raise(kvdp_last_error());
     slot_worker_.assign(kMaxWorkers, std::nullopt);
   }
@@ -88,8 +91,22 @@ class RadixTree {  // indexer.rs:187-387
       slot_worker_[slot].reset();
     }
   }
-  OverlapScores find_matches(const std::vector<uint64_t>& sequence, bool early_exit = false) {  // indexer.rs:239-277
-    return find_matches_batch({sequence}, early_exit)[0];
+  // indexer.rs:239-277. `now_s`: clock override for tests (default: steady clock)
+  OverlapScores find_matches(const std::vector<uint64_t>& sequence, bool early_exit = false,
+                             std::optional<double> now_s = std::nullopt) {
+    OverlapScores out = find_matches_batch({sequence}, early_exit)[0];
+    if (expiration_s_) {
+      const int64_t now_ns =
+          now_s ? (int64_t)(*now_s * 1e9 + 0.5)
+                : (int64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(
+                      std::chrono::steady_clock::now().time_since_epoch()).count();
+      std::vector<uint64_t> f(std::max<size_t>(sequence.size(), 1));
+      const int64_t n = kvdp_index_touch(ix_, sequence.data(), (int64_t)sequence.size(), early_exit ? 1 : 0, now_ns,
+                                         (int64_t)(*expiration_s_ * 1e9 + 0.5), f.data(), (int64_t)f.size());
+      if (n < 0) raise(kvdp_last_error());
+      out.frequencies.assign(f.begin(), f.begin() + n);
+    }
+    return out;
   }
   // Many requests in one launch (new).
   std::vector<OverlapScores> find_matches_batch(const std::vector<std::vector<uint64_t>>& sequences,
@@ -154,6 +171,7 @@ class RadixTree {  // indexer.rs:187-387
     return nw;
   }
   kvdp_index* ix_ = nullptr;
+  std::optional<double> expiration_s_;
   std::unordered_map<WorkerId, int> worker_slot_;
   std::vector<std::optional<WorkerId>> slot_worker_;
 };

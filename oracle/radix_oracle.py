@@ -6,7 +6,7 @@ Follows /root/reference/lib/llm/src/kv_router/indexer.rs:
     OverlapScores     :390-436
 Pure-Python dicts and sets, object identity standing in for the reference's Rc<RefCell<..>> sharing (a block reachable
 from several parents, or kept alive only by a worker's lookup table, behaves as it does there). The access-frequency
-feature (expiration_duration, :254-266) is left out: KvIndexer::new builds the tree without it.
+feature (expiration_duration, :251-267) is available through `find_matches_with_frequency`, with the clock passed in.
 
 Parity pin: the reference's own unit test `test_radix_tree` (indexer.rs:949-1170) is replayed in
 tests/test_oracle_radix.py, including its assertions on lookup-table and child counts.
@@ -17,11 +17,12 @@ from typing import Dict, List, Optional, Tuple
 
 
 class RadixBlock:
-    __slots__ = ("children", "workers")
+    __slots__ = ("children", "workers", "recent_uses")
 
     def __init__(self):
         self.children: Dict[int, "RadixBlock"] = {}
         self.workers: set = set()
+        self.recent_uses: List[float] = []
 
 
 class RadixTree:
@@ -43,6 +44,27 @@ class RadixTree:
                 break
             current = block
         return scores
+
+    # indexer.rs:239-277 with expiration_duration = Some(expiration): returns (scores, frequencies)
+    def find_matches_with_frequency(self, sequence: List[int], early_exit: bool, now: float, expiration: float):
+        scores: Dict[int, int] = {}
+        frequencies: List[int] = []
+        current = self.root
+        for h in sequence:
+            block = current.children.get(h)
+            if block is None:
+                break
+            for w in block.workers:
+                scores[w] = scores.get(w, 0) + 1
+            while block.recent_uses and now - block.recent_uses[0] > expiration:
+                block.recent_uses.pop(0)
+            if block.recent_uses:                       # add_frequency skips zeros (:429-436)
+                frequencies.append(len(block.recent_uses))
+            block.recent_uses.append(now)
+            if early_exit and len(block.workers) == 1:
+                break
+            current = block
+        return scores, frequencies
 
     # indexer.rs:284-378
     def apply_stored(self, worker_id: int, parent_hash: Optional[int], blocks: List[Tuple[int, int]]) -> bool:

@@ -111,6 +111,7 @@ extern "C" {
     pub fn kvdp_index_find_matches(ix: *mut KvdpIndex, d_hashes: *const u64, d_seq_offsets: *const i64, n_req: i64, early_exit: i32, num_workers: i32, d_scores: *mut u32, d_matched_depth: *mut i32, stream: *mut c_void) -> c_int;
     pub fn kvdp_index_find_matches_host(ix: *mut KvdpIndex, h_hashes: *const u64, h_seq_offsets: *const i64, n_req: i64, early_exit: i32, num_workers: i32, h_scores: *mut u32, h_matched_depth: *mut i32) -> c_int;
     pub fn kvdp_index_find_matches_for_tokens_host(ix: *mut KvdpIndex, h_tokens: *const u32, h_offsets: *const i64, n_req: i64, block_size: i32, early_exit: i32, num_workers: i32, h_scores: *mut u32, h_matched_depth: *mut i32) -> c_int;
+    pub fn kvdp_index_touch(ix: *mut KvdpIndex, h_hashes: *const u64, n: i64, early_exit: i32, now_ns: i64, expiration_ns: i64, h_frequencies: *mut u64, cap: i64) -> i64;
     pub fn kvdp_index_stat(ix: *mut KvdpIndex, what: i32, arg: u64) -> i64;
     // §I engine-facing KV-event ABI (same symbols as libdynamo_llm_capi.so)
     pub fn dynamo_llm_init(namespace_c_str: *const c_char, component_c_str: *const c_char, worker_id: i64, kv_block_size: u32) -> u32;

@@ -174,6 +174,17 @@ static void test_index() {  // indexer.rs:949-1150
   t2.apply_event(store_event(1, 0, {1}));
   CHECK(t2.find_matches({1, 2, 3}, true).scores[0] == 2 && t2.find_matches({1, 2, 3}, true).scores[1] == 1);
 
+  {  // indexer.rs:1305-1363 (test_frequency), clock passed in
+    RadixTree f(256, -1, 0.050);
+    f.apply_event(store_event(0, 0, {1, 2, 3, 4}));
+    CHECK(f.find_matches({1, 2, 3, 4}, false, 0.005).frequencies.empty());
+    CHECK((f.find_matches({1, 2, 3, 4}, false, 0.0051).frequencies == std::vector<size_t>{1, 1, 1, 1}));
+    CHECK(f.find_matches({1, 2, 3, 4}, false, 0.105).frequencies.empty());
+    CHECK((f.find_matches({1, 2, 3, 4}, false, 0.1051).frequencies == std::vector<size_t>{1, 1, 1, 1}));
+    CHECK((f.find_matches({1, 2, 3}, false, 0.1052).frequencies == std::vector<size_t>{2, 2, 2}));
+    CHECK((f.find_matches({1, 2, 3, 4}, false, 0.1053).frequencies == std::vector<size_t>{3, 3, 3, 2}));
+  }
+
   KvIndexerSharded sharded(3, 4, 1024);
   for (WorkerId w = 0; w < 100; ++w) sharded.apply_event(store_event(w, 0, {1, 2, (uint64_t)(10 + w)}));
   CHECK((sharded.worker_counts() == std::vector<size_t>{34, 33, 33}));

@@ -265,3 +265,43 @@ def test_worker_slots_are_recycled_when_nothing_stale_is_left(gpu):
     trie.remove_worker(8)
     assert 8 not in trie._slot
     trie.close()
+
+
+@pytest.mark.parametrize("num_shards", [1, 3])
+def test_frequency_reference_scenario_and_random_parity(gpu, num_shards):
+    """indexer.rs:1305-1363 (test_frequency, for KvIndexer and KvIndexerSharded) with an explicit clock, then a random
+    stream of lookups against the oracle's bookkeeping."""
+    exp = 0.050
+    ix = (KvIndexer.new_with_frequency(exp, 4, max_nodes=1024) if num_shards == 1
+          else KvIndexerSharded(num_shards, 4, max_nodes=1024, expiration_duration=exp))
+    ix.apply_event(store_event(0, 0, [1, 2, 3, 4]))
+    seq, now = [1, 2, 3, 4], 0.005
+    assert ix.find_matches(seq, now=now).frequencies == []
+    assert ix.find_matches(seq, now=now + 0.0001).frequencies == [1, 1, 1, 1]
+    now += 0.100
+    assert ix.find_matches(seq, now=now).frequencies == []
+    assert ix.find_matches(seq, now=now + 0.0001).frequencies == [1, 1, 1, 1]
+    assert ix.find_matches(seq[:3], now=now + 0.0002).frequencies == [2, 2, 2]
+    got = ix.find_matches(seq, now=now + 0.0003)
+    assert got.frequencies == [3, 3, 3, 2] and got.scores == {0: 4}
+    if num_shards > 1:
+        ix.shutdown()
+        return
+    # random parity on one tree: two workers, shared prefixes, lookups at random times
+    rng = np.random.default_rng(17)
+    tree, ref = RadixTree(max_nodes=4096, expiration_duration=exp), OracleTree()
+    docs = [[int(x) for x in rng.integers(1, 50, size=10)] for _ in range(5)]
+    for w in (0, 1):
+        for d in docs[w:w + 4]:
+            tree.apply_event(RouterEvent(w, KvCacheEvent(0, KvCacheStoreData(
+                None, [KvCacheStoredBlockData((h << 8) | w, h) for h in d]))))
+            ref.apply_stored(w, None, [((h << 8) | w, h) for h in d])
+    clock = 1.0
+    for _ in range(200):
+        clock += float(rng.choice([0.001, 0.004, 0.03, 0.2]))
+        q = docs[int(rng.integers(0, 5))][:int(rng.integers(1, 11))]
+        early = bool(rng.integers(0, 2))
+        want_scores, want_freq = ref.find_matches_with_frequency(q, early, clock, exp)
+        got = tree.find_matches(q, early, now=clock)
+        assert got.scores == {w: c for w, c in want_scores.items() if c} and got.frequencies == want_freq
+    tree.close()

@@ -72,3 +72,18 @@ def test_unknown_parent_skips_the_store_and_unknown_remove_is_ignored():
     remove(trie, 0, [1])                                        # last worker leaves block 1: its children are cleared
     assert trie.find_matches([1, 2], False) == {}
     assert 200 in trie.lookup[0]                                # block 2 lives on in the lookup table only
+
+
+def test_frequency_like_the_reference():
+    """indexer.rs:1305-1363 (test_frequency) with the clock passed in: 50 ms window; sleeps of 5 ms and 100 ms."""
+    t = RadixTree()
+    t.apply_stored(0, None, [(i * 100, i) for i in (1, 2, 3, 4)])
+    seq, exp = [1, 2, 3, 4], 0.050
+    now = 0.005
+    assert t.find_matches_with_frequency(seq, False, now, exp)[1] == []
+    assert t.find_matches_with_frequency(seq, False, now + 0.0001, exp)[1] == [1, 1, 1, 1]
+    now += 0.100
+    assert t.find_matches_with_frequency(seq, False, now, exp)[1] == []
+    assert t.find_matches_with_frequency(seq, False, now + 0.0001, exp)[1] == [1, 1, 1, 1]
+    assert t.find_matches_with_frequency(seq[:3], False, now + 0.0002, exp)[1] == [2, 2, 2]
+    assert t.find_matches_with_frequency(seq, False, now + 0.0003, exp)[1] == [3, 3, 3, 2]
