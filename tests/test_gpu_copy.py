@@ -531,3 +531,88 @@ def test_range_limits_are_reported_not_wrapped(gpu):
     assert rc == gpu.KVDP_ERANGE and "tiles in one launch" in gpu.last_error()
     assert gpu.lib().kvdp_plan_launch(h, ids.ptr, ids.ptr, 0, 0, 1, None) == 0                   # nothing to do
     gpu.lib().kvdp_plan_destroy(h)
+
+
+def _model_plan(desc, src_bufs, dst_bufs, sid, did, layer_begin, layer_end):
+    """Plain-Python statement of the kvdp_plan_desc address algebra (include/kvdp.h): for every layer, prefix, pair,
+    row and group one run of run_bytes."""
+    L, G = desc["num_layers"], desc["row_groups"]
+    for l in range(layer_begin, layer_end):
+        for p in range(desc["prefix_dim"]):
+            for s, d in zip(sid, did):
+                for r in range(desc["rows"]):
+                    for g in range(G):
+                        if desc["src_row_stride"]:
+                            so = (p * desc["src_prefix_stride"] + s * desc["src_block_stride"] + r * desc["src_row_stride"]
+                                  + desc["src_col_offset"] + g * desc["run_bytes"])
+                        else:
+                            so = (p * desc["src_prefix_stride"] + s * desc["src_block_stride"]
+                                  + (r * G + g) * desc["run_bytes"])
+                        do = (p * desc["dst_prefix_stride"] + d * desc["dst_block_stride"] + r * desc["dst_row_stride"]
+                              + desc["dst_col_offset"])
+                        dst_bufs[g * L + l][do:do + desc["run_bytes"]] = src_bufs[l][so:so + desc["run_bytes"]]
+
+
+@pytest.mark.parametrize("seed", range(30))
+def test_random_plan_geometries_against_the_address_algebra(gpu, seed):
+    """Fuzz over the whole descriptor space the kernels accept — run sizes 1 B..6 KiB at every alignment, 1..3 row groups,
+    dense and strided rows on either side, column offsets, several layers and prefixes, partial layer ranges — on every
+    copy path; destinations are pre-filled so that a stray write shows."""
+    rng = np.random.default_rng(1000 + seed)
+    for case in range(6):
+        align = int(rng.choice([1, 2, 4, 8, 16, 16, 16]))
+        run = int(rng.integers(1, 6144 // align + 1)) * align
+        if rng.random() < 0.4:
+            run = int(rng.choice([16, 64, 256, 512, 2048, 4096]))
+        G = int(rng.choice([1, 1, 2, 3]))
+        rows = int(rng.choice([1, 1, 2, 5, 16]))
+        L, prefix = int(rng.integers(1, 4)), int(rng.integers(1, 3))
+        n_src, n_dst, npairs = int(rng.integers(3, 9)), int(rng.integers(3, 9)), 0
+        npairs = int(rng.integers(1, min(n_src, n_dst) + 1))
+        src_strided = G == 1 and rng.random() < 0.35
+        pad = lambda v: (v + align - 1) // align * align
+        if src_strided:
+            src_row = pad(run + int(rng.integers(0, 3)) * align * 3)
+            src_col = int(rng.integers(0, (src_row - run) // align + 1)) * align
+            src_block = rows * src_row
+        else:
+            src_row, src_col, src_block = 0, 0, rows * G * run
+        dst_row = pad(run + int(rng.integers(0, 3)) * align * 5) if rng.random() < 0.6 else run
+        dst_col = int(rng.integers(0, (dst_row - run) // align + 1)) * align
+        dst_block = rows * dst_row
+        desc = dict(num_layers=L, row_groups=G, prefix_dim=prefix, rows=rows, run_bytes=run,
+                    src_prefix_stride=n_src * src_block, src_block_stride=src_block,
+                    dst_prefix_stride=n_dst * dst_block, dst_block_stride=dst_block, dst_row_stride=dst_row,
+                    dst_col_offset=dst_col, src_row_stride=src_row, src_col_offset=src_col)
+        src_np = [rng.integers(0, 255, size=prefix * n_src * src_block, dtype=np.uint8) for _ in range(L)]
+        dst_np = [rng.integers(0, 255, size=prefix * n_dst * dst_block, dtype=np.uint8) for _ in range(G * L)]
+        src_d = [DevBuf(gpu, a.nbytes) for a in src_np]
+        dst_d = [DevBuf(gpu, a.nbytes) for a in dst_np]
+        sid = [int(x) for x in rng.integers(0, n_src, size=npairs)]
+        did = [int(x) for x in rng.permutation(n_dst)[:npairs]]
+        lb = int(rng.integers(0, L))
+        le = int(rng.integers(lb + 1, L + 1))
+        d = gpu.PlanDesc()
+        for k, v in desc.items():
+            setattr(d, k, v)
+        sp = np.array([b.ptr for b in src_d], dtype=np.uint64)
+        dp = np.array([b.ptr for b in dst_d], dtype=np.uint64)
+        d.src_blocks, d.dst_blocks = n_src, n_dst
+        d.src_layer_ptrs, d.dst_layer_ptrs, d.device = sp.ctypes.data, dp.ctypes.data, -1
+        plan = CopyPlan.from_desc(d, keepalive=(sp, dp))
+        want = [a.copy() for a in dst_np]
+        _model_plan(desc, src_np, want, sid, did, lb, le)
+        eng = TransferEngine(npairs)
+        for path in (0, 1, 2, 3, 4):
+            gpu.set_option("copy_path", path)
+            gpu.set_option("tile_bytes", int(rng.choice([0, 1024, 4096])))
+            for b, a in zip(src_d, src_np):
+                b.upload(a)
+            for b, a in zip(dst_d, dst_np):
+                b.upload(a)
+            eng.run(plan, sid, did, layer_begin=lb, layer_end=le)
+            eng.sync()
+            for k, (b, w) in enumerate(zip(dst_d, want)):
+                assert np.array_equal(b.download(), w), (seed, case, path, k, desc)
+        plan.close()
+        eng.close()
