@@ -193,3 +193,24 @@ def test_stored_event_from_parts_like_the_c_bindings(gpu, oracle):
     want = oracle.indexer_block_hashes(toks[:3 * bs], bs)
     assert [b["tokens_hash"] for b in blocks] == [int(x) for x in want]
     assert kv_event_create_stored_from_parts(8, toks, [3], [1], bs)["data"]["stored"]["blocks"] == []
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_random_batches_block_sizes_and_salts_vs_oracle(gpu, oracle, seed):
+    """Fuzz: block sizes 1..300 tokens (every kernel: lane-parts, TMA rows, generic), random request lengths with many
+    empties and sub-block requests, random 64-bit salts."""
+    rng = np.random.default_rng(5000 + seed)
+    bs = int(rng.choice([1, 2, 3, 4, 5, 7, 8, 12, 16, 24, 32, 33, 48, 64, 100, 128, 200, 256, 300]))
+    n_req = int(rng.integers(1, 400))
+    lens = rng.integers(0, 12 * bs, size=n_req)
+    lens[rng.random(n_req) < 0.2] = 0
+    lens[rng.random(n_req) < 0.1] = bs - 1 if bs > 1 else 0
+    if seed % 5 == 0:
+        lens[int(rng.integers(0, n_req))] = 3000 * bs // max(1, bs // 4)       # one long request
+    offs = np.zeros(n_req + 1, dtype=np.int64)
+    offs[1:] = np.cumsum(lens)
+    toks = rng.integers(0, 2 ** 32, size=int(offs[-1]), dtype=np.uint64).astype(np.uint32)
+    salt = int(rng.integers(0, 2 ** 63)) * 2 + int(rng.integers(0, 2))
+    boff, bh, sh = hash_token_blocks(toks, offs, bs, salt)
+    w_off, w_bh, w_sh = oracle.hash_batch(toks, offs, bs, salt, threads=4)
+    assert np.array_equal(boff, w_off) and np.array_equal(bh, w_bh) and np.array_equal(sh, w_sh), (bs, n_req, salt)
