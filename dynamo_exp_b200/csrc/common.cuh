@@ -42,6 +42,9 @@ struct DevInfo {
 };
 int device_info(int device, DevInfo* out);
 
+// the event publisher stops feeding an index that is about to be destroyed (event_capi.cu)
+void event_sink_forget_index(const void* index);
+
 // RAII device switch
 struct DeviceGuard {
   int prev = -1;

@@ -198,6 +198,17 @@ int enqueue(Pending&& e, const uint32_t* toks, size_t ntok) {
 
 }  // namespace
 
+namespace kvdp {
+// Called by kvdp_index_destroy: if the publisher's sink is this index, wait for the batch in flight and detach.
+void event_sink_forget_index(const void* index) {
+  Publisher& p = pub();
+  std::unique_lock<std::mutex> lk(p.mu);
+  if (p.ix != index) return;
+  p.cv_idle.wait(lk, [&] { return p.delivered == p.submitted; });
+  p.ix = nullptr;
+}
+}  // namespace kvdp
+
 extern "C" {
 
 // lib.rs:50-113. The reference keeps its publisher in a process-wide OnceCell, so a second init returns OK and changes

@@ -270,6 +270,7 @@ int kvdp_index_create(kvdp_index** out, int64_t max_nodes, int32_t max_workers, 
 
 int kvdp_index_destroy(kvdp_index* ix) {
   if (!ix) return 0;
+  event_sink_forget_index(ix);  // an attached event publisher must not keep writing into freed memory
   DeviceGuard g(ix->device);
   if (ix->stream) {
     cudaStreamSynchronize(ix->stream);

@@ -333,7 +333,7 @@ dynamo_llm_result_t dynamo_kv_event_publish_removed(uint64_t event_id, const uin
                                                     size_t num_blocks);                       /* lib.rs:297-311 */
 /* Sinks (no reference counterpart). A callback receives every event as (subject, RouterEvent JSON, length) on the
  * publisher thread; an index sink applies the events to a prefix index under worker slot `worker_slot` (either, both or
- * neither may be set; pass NULL to clear). With neither, events wait in an outbox of 65 536 entries for
+ * neither may be set; pass NULL to clear; kvdp_index_destroy detaches an index that is still attached). With neither, events wait in an outbox of 65 536 entries for
  * kvdp_event_poll: returns 1 and copies one event (not NUL-terminated, *len bytes), 0 when empty, KVDP_ERANGE with
  * *len = bytes needed when `cap` is too small. kvdp_event_flush blocks until every event published so far has been
  * hashed and delivered. kvdp_event_stat: 0 submitted, 1 delivered, 2 hash batches, 3 blocks hashed, 4 short blocks

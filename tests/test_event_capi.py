@@ -221,3 +221,21 @@ def test_event_stream_into_the_prefix_index_matches_the_oracle_tree(gpu, capi, o
     pub.attach_index(None)
     pub.shutdown()
     tree.close()
+
+
+@pytest.mark.gpu
+def test_destroying_an_attached_index_detaches_it(gpu, capi):
+    """An engine that tears its index down while the publisher still points at it must not crash: destroy detaches
+    the sink after the batch in flight; later events go to the outbox."""
+    from dynamo_exp_b200.indexer import RadixTree
+    tree = RadixTree(max_nodes=256)
+    pub = KvEventPublisher("ns/c", 3, 4)
+    pub.attach_index(tree)
+    for ev in range(50):
+        pub.publish_stored(ev, [ev, 1, 2, 3], [4], [ev + 1], 0)
+    tree.close()                                                 # waits for the queued events, then detaches
+    pub.publish_removed(99, [1])
+    pub.flush()
+    got = pub.poll()
+    assert got is not None and got.event.event_id == 99
+    pub.shutdown()
