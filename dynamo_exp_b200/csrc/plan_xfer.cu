@@ -210,10 +210,23 @@ static int check_ids(const kvdp_plan* p, const int32_t* s, const int32_t* d, int
       return fail(KVDP_EINVAL, "destination block id %d (pair %d) outside [0,%lld)", d[i], i, (long long)db);
   }
   if (flags & KVDP_XFER_CHECK_DST_UNIQUE) {
-    std::vector<int32_t> v(d, d + n);
-    std::sort(v.begin(), v.end());
-    if (std::adjacent_find(v.begin(), v.end()) != v.end())
-      return fail(KVDP_EDUP, "duplicate destination block id: two pairs would write the same block");
+    if (db > 0 && (db >> 6) <= 8 * (int64_t)n + 1024) {  // clearing the bitmap must not cost more than the pass
+      // ids are bounded (checked above): one pass over a bitmap, which matters for token-granular plans where n is
+      // tens of thousands per call
+      static thread_local std::vector<uint64_t> seen;
+      seen.assign((size_t)((db + 63) / 64), 0);
+      for (int i = 0; i < n; ++i) {
+        uint64_t& w = seen[(size_t)d[i] >> 6];
+        const uint64_t bit = 1ULL << (d[i] & 63);
+        if (w & bit) return fail(KVDP_EDUP, "duplicate destination block id: two pairs would write the same block");
+        w |= bit;
+      }
+    } else {
+      std::vector<int32_t> v(d, d + n);
+      std::sort(v.begin(), v.end());
+      if (std::adjacent_find(v.begin(), v.end()) != v.end())
+        return fail(KVDP_EDUP, "duplicate destination block id: two pairs would write the same block");
+    }
   }
   return 0;
 }
