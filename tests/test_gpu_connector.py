@@ -261,3 +261,12 @@ def test_token_granular_transfer_all_layers_one_launch(gpu, L, Hs, Hd, D, E, h_s
         transfer_token_rows([src[0].ptr], [dst[0].ptr], [0], [ns_dst], ns_src, ns_dst, srow, drow)
     with pytest.raises(KvError):
         transfer_token_rows([src[0].ptr], [dst[0].ptr], [0], [0], ns_src, ns_dst, srow, drow, col_bytes=drow + 1)
+
+
+def test_disaggregated_flow_end_to_end_two_processes(gpu):
+    """tests/mp_disagg_flow.py: request planning, GPU hashing, prefix reuse, IPC push with completion tracking, KV events
+    through the engine ABI and the router's prefix index, decode and prefill engines as separate processes."""
+    script = os.path.join(os.path.dirname(__file__), "mp_disagg_flow.py")
+    r = subprocess.run([sys.executable, script], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "DISAGG FLOW OK" in r.stdout
