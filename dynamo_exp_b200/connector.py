@@ -477,6 +477,32 @@ class DynamoKvdpConnector:
         self._transfers[notify_msg] = self._xfer_seq
         self._engine.signal(self._host + MAILBOX_SLOTS * SLOT_BYTES, self._xfer_seq)
 
+    def write_token_rows(self, local_slots, remote_slots, dst_engine_id: str, notify_msg: str) -> None:
+        """Token-granular form of write_blocks: `slot = block * block_size + offset` on either side, every layer, K and
+        V, with the same TP head resharding, in one launch per request. This is the KV half of the reference's NCCL
+        connector (`send_kv_caches_and_hidden_states` / `recv_...`, patch:1602-1766: per layer a gather by
+        `slot_mapping` with a head slice, a send, and `reshape_and_cache_flash` on the other side). Asynchronous,
+        completion and notification as for write_blocks."""
+        rem = self._remote(dst_engine_id)
+        if self._is_mla:
+            raise KvError("token-granular transfer of the MLA latent cache is not implemented")
+        local_slots, remote_slots = list(local_slots), list(remote_slots)
+        if len(local_slots) != len(remote_slots):
+            raise KvError("local and remote slot lists must have the same length")
+        if local_slots:
+            if getattr(rem, "push_tokens", None) is None:
+                # the block reshard plan with one-token "blocks": rows = 1, runs of one (sub-)row
+                rem.push_tokens = CopyPlan.reshard(
+                    self._layer_ptrs, [rem.layer_ptrs[q] for q in rem.targets], self.num_blocks * self.block_size,
+                    rem.num_blocks * self.block_size, 1, self.block_len // self.block_size,
+                    self._tp_size[self.engine_id], rem.tp, self.rank, self.device)
+            self._engine.run(rem.push_tokens, local_slots, remote_slots, num_layers=self.num_layers)
+        for q in rem.targets:
+            self._post(dst_engine_id, q, rem.mailbox[q], notify_msg)
+        self._xfer_seq += 1
+        self._transfers[notify_msg] = self._xfer_seq
+        self._engine.signal(self._host + MAILBOX_SLOTS * SLOT_BYTES, self._xfer_seq)
+
     def read_blocks(self, local_block_ids, staging_block_ids, remote_block_ids, dst_engine_id: str) -> None:
         """reference: patch:1296-1359. Blocking, like the reference (it polls the NIXL handles to DONE)."""
         rem = self._remote(dst_engine_id)

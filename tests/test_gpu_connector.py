@@ -81,6 +81,39 @@ def test_write_blocks_reshards_and_notifies(gpu, ptp, dtp):
         c.shutdown()
 
 
+@pytest.mark.parametrize("ptp,dtp", [(1, 1), (1, 2), (2, 4), (1, 4), (4, 2), (2, 1), (4, 1), (2, 2)])
+def test_write_token_rows_reshards_per_token(gpu, ptp, dtp):
+    """The NCCL connector's KV path (patch:1602-1766) as one launch: decode.reshape(2, slots, Hq, D)[kv, dst_slot] =
+    prefill.reshape(2, slots, Hp, D)[kv, src_slot, head slice] for every layer; untouched slots keep their content."""
+    rng = np.random.Generator(np.random.PCG64(ptp * 31 + dtp))
+    canon = rng.integers(0, 2 ** 15, size=(L, 2, NP, BS, H, D), dtype=np.int16)
+    pre, pre_bufs, _ = make_engine(gpu, "prefill", ptp, NP, canon)
+    dec, dec_bufs, dec_meta = make_engine(gpu, "decode", dtp, ND)
+    before = [read_rank(dec_bufs, q, dtp, ND) for q in range(dtp)]
+    src_slots = [int(x) for x in rng.permutation(NP * BS)[:37]]
+    dst_slots = [int(x) for x in rng.permutation(ND * BS)[:37]]
+    for c in pre:
+        c.add_remote_agent("decode", dec_meta.agent_metadata, dtp, dec_meta.kv_caches_base_addr, dec_meta.num_blocks)
+        c.write_token_rows(src_slots, dst_slots, "decode", f"tok-{c.rank}")
+    for c in pre:
+        c.sync()
+        assert c.get_done_tranfers() == [f"tok-{c.rank}"]
+    hq = H // dtp
+    flat_canon = canon.reshape(L, 2, NP * BS, H, D)
+    for q in range(dtp):
+        got = read_rank(dec_bufs, q, dtp, ND)
+        for l in range(L):
+            want = before[q][l].reshape(2, ND * BS, hq, D).copy()
+            want[:, dst_slots] = flat_canon[l][:, src_slots][:, :, q * hq:(q + 1) * hq, :]
+            assert np.array_equal(got[l].reshape(2, ND * BS, hq, D), want), (q, l)
+        senders = sorted(p for p in range(ptp) if q in tp_targets(ptp, dtp, p))
+        assert dec[q].get_new_notifs() == {str(p): [f"tok-{p}"] for p in senders}
+    with pytest.raises(KvError):
+        pre[0].write_token_rows([0, 1], [0], "decode", "bad")
+    for c in pre + dec:
+        c.shutdown()
+
+
 @pytest.mark.parametrize("ptp,dtp", [(1, 1), (1, 2), (2, 4), (4, 2), (2, 1), (4, 1)])
 def test_read_blocks_pulls_and_inverts_the_reshard(gpu, ptp, dtp):
     """read_blocks (patch:1296-1359): the prefill side pulls prefix-hit blocks out of the decode caches. Any TP ratio,
