@@ -50,7 +50,7 @@ def main():
     import torch.distributed as dist
 
     from dynamo_exp_b200 import _lib as lib, build
-    from dynamo_exp_b200.connector import HEADS_BYTES, DynamoKvdpConnector, _head_off, tp_targets
+    from dynamo_exp_b200.connector import DynamoKvdpConnector, _head_off, tp_targets
     build.build()
     world = int(os.environ["WORLD_SIZE"])
     rank = int(os.environ["RANK"])

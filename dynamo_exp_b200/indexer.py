@@ -17,7 +17,7 @@ import numpy as np
 
 from . import _lib
 from .storage import KvError
-from .tokens import XXH3_SEED, _as_u32
+from .tokens import _as_u32
 
 WorkerId = int
 MAX_WORKERS = 64

@@ -16,7 +16,7 @@ library's outbox for `poll()`.
 from __future__ import annotations
 
 import ctypes as C
-from typing import Callable, List, Optional, Sequence, Tuple, Union
+from typing import Callable, Optional, Sequence, Tuple
 
 import numpy as np
 

@@ -8,12 +8,12 @@ peer/flag helpers replace what the patched vLLM connector does with Triton + NIX
 from __future__ import annotations
 
 import ctypes as C
-from typing import List, Optional, Sequence
+from typing import Optional, Sequence
 
 import numpy as np
 
 from . import _lib
-from .layer import KvBlockStorage, KvLayout, _ids32
+from .layer import KvBlockStorage, _ids32
 from .storage import CudaPinnedMemory, DeviceStorageOwned, KvError, Storage, StorageType
 
 
