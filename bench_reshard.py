@@ -50,7 +50,7 @@ def main():
     import torch.distributed as dist
 
     from dynamo_exp_b200 import _lib as lib, build
-    from dynamo_exp_b200.connector import DynamoKvdpConnector, _head_off, tp_targets
+    from dynamo_exp_b200.connector import DynamoKvdpConnector, tp_targets
     build.build()
     world = int(os.environ["WORLD_SIZE"])
     rank = int(os.environ["RANK"])
@@ -120,7 +120,7 @@ def main():
                 senders = [p for p in range(P) if tp_rank in tp_targets(P, D, p)]
                 for p in senders:   # one mailbox lane per sending prefill rank; its head counts delivered messages
                     lib.check(L.kvdp_stream_wait_flag(C.c_void_p(wait_stream.cuda_stream),
-                                                      C.c_void_p(conn._mailbox + _head_off(p)), sent["n"]))
+                                                      C.c_void_p(conn.notif_head_ptr("prefill:%d" % p)), sent["n"]))
         else:
             if not is_prefill:
                 for k in range(count):

@@ -12,7 +12,10 @@ What changes underneath:
     process); WRITE = kernel on this GPU storing into the peer, READ = kernel on this GPU loading from the peer;
   * decode TP smaller than prefill TP is supported (the reference asserts against it, patch:1437);
   * notifications: after a write the sender drops `notify_msg` into a mailbox ring in the receiver's device memory
-    and bumps the ring head with a system-scope release store, all in stream order behind the data.
+    and bumps the ring head with a system-scope release store, all in stream order behind the data. Every sending
+    agent (engine id + rank) claims a lane of its own in each receiver it talks to, so any number of prefill engines
+    can feed one decode engine and one prefill engine can feed several; a sender never overwrites a slot the receiver
+    has not read (it waits on the receiver's consumed counter instead).
 """
 from __future__ import annotations
 
@@ -28,20 +31,35 @@ from . import _lib
 from .storage import KvError
 from .transfer import CopyPlan, TransferEngine
 
-MAILBOX_LANES = 64          # one lane per sender TP rank
+MAILBOX_LANES = 64          # senders one receiver rank can hear from at a time (each claims its own lane)
 MAILBOX_SLOTS = 64          # ring depth per lane
-SLOT_BYTES = 128            # u32 len | u32 seq | 120 bytes of message
-HEADS_BYTES = MAILBOX_LANES * 64                       # one 64-byte line per lane head, all heads contiguous
-MAILBOX_BYTES = HEADS_BYTES + MAILBOX_LANES * MAILBOX_SLOTS * SLOT_BYTES
-MAX_MSG = SLOT_BYTES - 8
+SLOT_BYTES = 256            # u32 msg_len | u32 seq | u32 name_len | u32 0 | 48 bytes sender agent name | 192 bytes message
+NAME_BYTES = 48
+MAX_MSG = SLOT_BYTES - 16 - NAME_BYTES
+CLAIMS_BYTES = MAILBOX_LANES * 8                       # u64 key of the sender that owns the lane, 0 = free
+HEADS_OFF = CLAIMS_BYTES
+HEADS_BYTES = MAILBOX_LANES * 64                       # one 64-byte line per lane head (u32 messages delivered)
+CONSUMED_OFF = HEADS_OFF + HEADS_BYTES
+CONSUMED_BYTES = MAILBOX_LANES * 4                     # u32 messages the receiver has read, per lane (flow control)
+SLOTS_OFF = CONSUMED_OFF + CONSUMED_BYTES
+MAILBOX_BYTES = SLOTS_OFF + MAILBOX_LANES * MAILBOX_SLOTS * SLOT_BYTES
+STAGE_SLOTS = 64            # sender-side pinned staging ring, shared by every peer of this connector
 
 
 def _head_off(lane: int) -> int:
-    return lane * 64
+    return HEADS_OFF + lane * 64
 
 
 def _slot_off(lane: int, slot: int) -> int:
-    return HEADS_BYTES + (lane * MAILBOX_SLOTS + slot) * SLOT_BYTES
+    return SLOTS_OFF + (lane * MAILBOX_SLOTS + slot) * SLOT_BYTES
+
+
+def _agent_key(name: str) -> int:
+    """Non-zero 64-bit FNV-1a of a sender's agent name: what a lane's claim word holds."""
+    h = 0xCBF29CE484222325
+    for b in name.encode("utf-8"):
+        h = ((h ^ b) * 0x100000001B3) & 0xFFFFFFFFFFFFFFFF
+    return h or 1
 
 
 @dataclass
@@ -271,6 +289,7 @@ class _Remote:
     targets: List[int]
     layer_ptrs: Dict[int, List[int]] = field(default_factory=dict)    # target rank -> per-layer base pointers
     mailbox: Dict[int, int] = field(default_factory=dict)             # target rank -> mailbox base
+    lane: Dict[int, int] = field(default_factory=dict)                # target rank -> the lane this sender claimed there
     mapped: List[int] = field(default_factory=list)                   # IPC mappings to close
     push: Optional[CopyPlan] = None
     pull: List[CopyPlan] = field(default_factory=list)
@@ -300,16 +319,21 @@ class DynamoKvdpConnector:
         _lib.check(L.kvdp_device_alloc(C.byref(p), MAILBOX_BYTES, device))
         self._mailbox = p.value
         self._seen = [0] * MAILBOX_LANES
-        # sender-side: pinned message staging ring + a pinned progress word the stream bumps after each transfer
+        # sender-side: pinned message staging ring (shared by all peers, recycled against the progress word) + a pinned
+        # progress word the stream bumps after each transfer
         hp = C.c_void_p()
-        _lib.check(L.cuda_malloc_host(C.byref(hp), MAILBOX_SLOTS * SLOT_BYTES + 64))
+        _lib.check(L.cuda_malloc_host(C.byref(hp), STAGE_SLOTS * SLOT_BYTES + 64))
         self._host = hp.value
-        C.memset(self._host, 0, MAILBOX_SLOTS * SLOT_BYTES + 64)
-        self._progress = np.frombuffer((C.c_uint32 * 16).from_address(self._host + MAILBOX_SLOTS * SLOT_BYTES),
+        C.memset(self._host, 0, STAGE_SLOTS * SLOT_BYTES + 64)
+        self._progress = np.frombuffer((C.c_uint32 * 16).from_address(self._host + STAGE_SLOTS * SLOT_BYTES),
                                        dtype=np.uint32)
-        self._send_seq: Dict[tuple, int] = {}     # (engine, target rank) -> messages sent on that lane
+        self._send_seq: Dict[tuple, int] = {}     # (engine, target rank) -> messages sent on the lane claimed there
+        self._peer_consumed: Dict[tuple, int] = {}  # (engine, target rank) -> receiver's consumed count, as last read
+        self._stage_n = 0                         # staging slots handed out so far
+        self._stage_cover = [0] * STAGE_SLOTS     # transfer sequence number whose completion frees the slot
         self._xfer_seq = 0
         self._transfers: Dict[str, int] = {}      # notify_msg -> local sequence number
+        self.notify_timeout_s = 30.0              # how long a sender waits for a receiver that does not drain its ring
 
     # ---------------------------------------------------------------------------------------------- registration
     @property
@@ -400,6 +424,12 @@ class DynamoKvdpConnector:
                 _lib.check(L.kvdp_peer_enable(self.device, m["device"]))
             rem.layer_ptrs[q] = [open_ptr(m, h, raw) for h, raw in zip(m["layers"], m["layer_ptrs"])]
             rem.mailbox[q] = open_ptr(m, m["mailbox"], m["mailbox_ptr"])
+            rem.lane[q] = self._claim_lane(rem.mailbox[q])
+            # a sender that comes back under the same name continues the lane's numbering instead of restarting at 1
+            word = np.zeros(1, dtype=np.uint32)
+            _lib.check(L.cuda_memcpy_sync(C.c_void_p(word.ctypes.data),
+                                          C.c_void_p(rem.mailbox[q] + _head_off(rem.lane[q])), 4))
+            self._send_seq[(engine_id, q)] = max(self._send_seq.get((engine_id, q), 0), int(word[0]))
         self.kv_caches_base_addr[engine_id] = kv_caches_base_addr
         self._remotes[engine_id] = rem
         self._build_plans(engine_id, rem, metas)
@@ -472,10 +502,10 @@ class DynamoKvdpConnector:
             else:
                 self._engine.run(rem.push, local_block_ids, remote_block_ids, num_layers=self.num_layers)
         for q in rem.targets:                                              # empty => notify only (patch:1373-1377)
-            self._post(dst_engine_id, q, rem.mailbox[q], notify_msg)
+            self._post(dst_engine_id, q, rem, notify_msg)
         self._xfer_seq += 1
         self._transfers[notify_msg] = self._xfer_seq
-        self._engine.signal(self._host + MAILBOX_SLOTS * SLOT_BYTES, self._xfer_seq)
+        self._engine.signal(self._host + STAGE_SLOTS * SLOT_BYTES, self._xfer_seq)
 
     def write_token_rows(self, local_slots, remote_slots, dst_engine_id: str, notify_msg: str) -> None:
         """Token-granular form of write_blocks: `slot = block * block_size + offset` on either side, every layer, K and
@@ -498,10 +528,10 @@ class DynamoKvdpConnector:
                     self._tp_size[self.engine_id], rem.tp, self.rank, self.device)
             self._engine.run(rem.push_tokens, local_slots, remote_slots, num_layers=self.num_layers)
         for q in rem.targets:
-            self._post(dst_engine_id, q, rem.mailbox[q], notify_msg)
+            self._post(dst_engine_id, q, rem, notify_msg)
         self._xfer_seq += 1
         self._transfers[notify_msg] = self._xfer_seq
-        self._engine.signal(self._host + MAILBOX_SLOTS * SLOT_BYTES, self._xfer_seq)
+        self._engine.signal(self._host + STAGE_SLOTS * SLOT_BYTES, self._xfer_seq)
 
     def read_blocks(self, local_block_ids, staging_block_ids, remote_block_ids, dst_engine_id: str) -> None:
         """reference: patch:1296-1359. Blocking, like the reference (it polls the NIXL handles to DONE)."""
@@ -518,27 +548,93 @@ class DynamoKvdpConnector:
                              check_dst_unique=True)
         self._engine.sync()
 
-    def _post(self, engine_id: str, target_rank: int, mailbox_ptr: int, msg: str) -> None:
+    def _claim_lane(self, mailbox_ptr: int) -> int:
+        """Take (or find again) this sender's lane in a receiver's mailbox: a system-scope CAS on the lane's claim
+        word, probing from hash(agent_name). Every (engine, rank) that writes to a receiver gets a lane of its own there,
+        like NIXL's per-agent notification queues, so two prefill engines with equal rank numbers never share one."""
+        L = _lib.lib()
+        key = _agent_key(self.agent_name)
+        for probe in range(MAILBOX_LANES):
+            lane = (key + probe) % MAILBOX_LANES
+            old = C.c_uint64(0)
+            _lib.check(L.kvdp_flag_cas64(C.c_void_p(mailbox_ptr + lane * 8), 0, key, C.byref(old), self.device))
+            if old.value in (0, key):
+                return lane
+        raise KvError(f"all {MAILBOX_LANES} notification lanes of the receiver are taken")
+
+    def notif_head_ptr(self, sender_agent_name: str) -> int:
+        """Receiver side: device address of the u32 that counts the messages `sender_agent_name` has delivered here (0 if
+        that sender has not added this agent yet). A stream can wait on it with kvdp_stream_wait_flag."""
+        claims = np.zeros(MAILBOX_LANES, dtype=np.uint64)
+        _lib.check(_lib.lib().cuda_memcpy_sync(C.c_void_p(claims.ctypes.data), C.c_void_p(self._mailbox), CLAIMS_BYTES))
+        key = _agent_key(sender_agent_name)
+        for probe in range(MAILBOX_LANES):
+            lane = (key + probe) % MAILBOX_LANES
+            if int(claims[lane]) == key:
+                return self._mailbox + _head_off(lane)
+            if int(claims[lane]) == 0:
+                return 0
+        return 0
+
+    def _stage_slot(self) -> int:
+        """Next pinned staging slot. A slot is free again once the transfer whose stream position covers its upload has
+        completed, which the pinned progress word shows without any stream synchronisation."""
+        slot = self._stage_n % STAGE_SLOTS
+        self._stage_n += 1
+        need = self._stage_cover[slot]
+        if need and int(self._progress[0]) < need:
+            import time
+            deadline = time.monotonic() + self.notify_timeout_s
+            while int(self._progress[0]) < need:
+                if time.monotonic() > deadline:
+                    raise KvError("notification staging ring did not drain (stream stalled?)")
+                time.sleep(0)
+        self._stage_cover[slot] = self._xfer_seq + 1     # the signal the current write call enqueues last
+        return slot
+
+    def _wait_for_room(self, key, rem: _Remote, target_rank: int, seq: int) -> None:
+        """Flow control: never overwrite a ring slot the receiver has not read. The receiver publishes how many messages
+        it has consumed per lane; it is re-read only when the cached value says the ring could be full."""
+        if seq - self._peer_consumed.get(key, 0) <= MAILBOX_SLOTS:
+            return
+        import time
+        L = _lib.lib()
+        word = np.zeros(1, dtype=np.uint32)
+        addr = rem.mailbox[target_rank] + CONSUMED_OFF + rem.lane[target_rank] * 4
+        deadline = time.monotonic() + self.notify_timeout_s
+        while True:
+            _lib.check(L.cuda_memcpy_sync(C.c_void_p(word.ctypes.data), C.c_void_p(addr), 4))
+            self._peer_consumed[key] = int(word[0])
+            if seq - int(word[0]) <= MAILBOX_SLOTS:
+                return
+            if time.monotonic() > deadline:
+                raise KvError(f"{key[0]}:{target_rank} has {MAILBOX_SLOTS} unread notifications from {self.agent_name}: "
+                              "it must call get_new_notifs()")
+            time.sleep(0.0005)
+
+    def _post(self, engine_id: str, target_rank: int, rem: _Remote, msg: str) -> None:
         data = msg.encode("utf-8")
         if len(data) > MAX_MSG:
             raise KvError(f"notify message longer than {MAX_MSG} bytes")
+        name = self.agent_name.encode("utf-8")[:NAME_BYTES]
         key = (engine_id, target_rank)
         seq = self._send_seq.get(key, 0) + 1
+        self._wait_for_room(key, rem, target_rank, seq)
         self._send_seq[key] = seq
         slot = (seq - 1) % MAILBOX_SLOTS
-        # the pinned staging slot may still be in flight from MAILBOX_SLOTS messages ago
-        if seq > MAILBOX_SLOTS:
-            self._engine.sync()
-        rec = np.frombuffer((C.c_uint8 * SLOT_BYTES).from_address(self._host + slot * SLOT_BYTES), dtype=np.uint8)
+        stage = self._stage_slot()
+        rec = np.frombuffer((C.c_uint8 * SLOT_BYTES).from_address(self._host + stage * SLOT_BYTES), dtype=np.uint8)
         rec[:] = 0
-        rec[:8].view(np.uint32)[:] = (len(data), seq)
-        rec[8:8 + len(data)] = np.frombuffer(data, dtype=np.uint8)
+        rec[:16].view(np.uint32)[:] = (len(data), seq, len(name), 0)
+        rec[16:16 + len(name)] = np.frombuffer(name, dtype=np.uint8)
+        rec[16 + NAME_BYTES:16 + NAME_BYTES + len(data)] = np.frombuffer(data, dtype=np.uint8)
         L = _lib.lib()
-        _lib.check(L.cuda_memcpy_async(C.c_void_p(mailbox_ptr + _slot_off(self.rank, slot)),
-                                       C.c_void_p(self._host + slot * SLOT_BYTES), SLOT_BYTES,
+        mailbox_ptr, lane = rem.mailbox[target_rank], rem.lane[target_rank]
+        _lib.check(L.cuda_memcpy_async(C.c_void_p(mailbox_ptr + _slot_off(lane, slot)),
+                                       C.c_void_p(self._host + stage * SLOT_BYTES), SLOT_BYTES,
                                        C.c_void_p(self._engine.stream)))
         # release store of the lane head, ordered after data and message
-        self._engine.signal(mailbox_ptr + _head_off(self.rank), seq)
+        self._engine.signal(mailbox_ptr + _head_off(lane), seq)
 
     def get_done_tranfers(self) -> List[str]:
         """Sender side: request ids whose transfer (data + notification) has completed (reference: patch:1473-1492)."""
@@ -549,30 +645,36 @@ class DynamoKvdpConnector:
         return done
 
     def get_new_notifs(self) -> Dict[str, List[str]]:
-        """Receiver side: messages that arrived since the last call, keyed by sender rank (reference: patch:1421-1425
-        returns NIXL's {agent_name: [notifs]})."""
+        """Receiver side: messages that arrived since the last call, keyed by the sender's agent name
+        (`<engine_id>:<rank>`), as NIXL's get_new_notifs returns {agent_name: [notifs]} (reference: patch:1421-1425)."""
         L = _lib.lib()
         out: Dict[str, List[str]] = {}
         heads = np.zeros(HEADS_BYTES // 4, dtype=np.uint32)
-        _lib.check(L.cuda_memcpy_sync(C.c_void_p(heads.ctypes.data), C.c_void_p(self._mailbox), HEADS_BYTES))
+        _lib.check(L.cuda_memcpy_sync(C.c_void_p(heads.ctypes.data), C.c_void_p(self._mailbox + HEADS_OFF),
+                                      HEADS_BYTES))
         lane_heads = heads[::16]
         for lane in range(MAILBOX_LANES):
             head = int(lane_heads[lane])
-            if head <= self._seen[lane]:
+            seen = self._seen[lane]
+            if head <= seen:
                 continue
-            msgs = []
-            first = max(self._seen[lane] + 1, head - MAILBOX_SLOTS + 1)
-            for seq in range(first, head + 1):
-                slot = (seq - 1) % MAILBOX_SLOTS
-                rec = np.zeros(SLOT_BYTES, dtype=np.uint8)
-                _lib.check(L.cuda_memcpy_sync(C.c_void_p(rec.ctypes.data),
-                                              C.c_void_p(self._mailbox + _slot_off(lane, slot)), SLOT_BYTES))
-                n, s = [int(x) for x in rec[:8].view(np.uint32)]
-                if s == seq:
-                    msgs.append(bytes(rec[8:8 + n]).decode("utf-8"))
+            if head - seen > MAILBOX_SLOTS:
+                raise KvError(f"notification lane {lane} overran: {head - seen} unread messages in a ring of "
+                              f"{MAILBOX_SLOTS} (a sender ignored the consumed counter)")
+            ring = np.zeros(MAILBOX_SLOTS * SLOT_BYTES, dtype=np.uint8)
+            _lib.check(L.cuda_memcpy_sync(C.c_void_p(ring.ctypes.data), C.c_void_p(self._mailbox + _slot_off(lane, 0)),
+                                          ring.nbytes))
+            for seq in range(seen + 1, head + 1):
+                rec = ring[((seq - 1) % MAILBOX_SLOTS) * SLOT_BYTES:][:SLOT_BYTES]
+                n, s, nn, _ = [int(x) for x in rec[:16].view(np.uint32)]
+                if s != seq:
+                    raise KvError(f"notification lane {lane}: slot holds message {s}, expected {seq}")
+                sender = bytes(rec[16:16 + nn]).decode("utf-8")
+                out.setdefault(sender, []).append(bytes(rec[16 + NAME_BYTES:16 + NAME_BYTES + n]).decode("utf-8"))
             self._seen[lane] = head
-            if msgs:
-                out[str(lane)] = msgs
+            word = np.array([head], dtype=np.uint32)      # lets the sender reuse the slots just read
+            _lib.check(L.cuda_memcpy_sync(C.c_void_p(self._mailbox + CONSUMED_OFF + lane * 4),
+                                          C.c_void_p(word.ctypes.data), 4))
         return out
 
     def sync(self) -> None:

@@ -55,6 +55,14 @@ __global__ void kvdp_signal_kernel(uint32_t* flag, uint32_t value) {
 }
 }  // namespace
 
+// result slot of kvdp_flag_cas64 (one per device that loads the library; calls are serialised by a mutex)
+__device__ unsigned long long g_cas_old;
+namespace {
+__global__ void kvdp_cas64_kernel(unsigned long long* addr, unsigned long long expected, unsigned long long desired) {
+  g_cas_old = atomicCAS_system(addr, expected, desired);
+}
+}  // namespace
+
 int enqueue_signal(uint32_t* flag, uint32_t value, cudaStream_t stream) {
   kvdp_signal_kernel<<<1, 1, 0, stream>>>(flag, value);
   KVDP_CUDA(cudaGetLastError());
@@ -220,6 +228,20 @@ int kvdp_ipc_import(const uint8_t handle[KVDP_IPC_HANDLE_BYTES], int32_t device,
 int kvdp_ipc_close(void* mapped_ptr) {
   if (!mapped_ptr) return 0;
   KVDP_CUDA(cudaIpcCloseMemHandle(mapped_ptr));
+  return 0;
+}
+
+int kvdp_flag_cas64(uint64_t* addr, uint64_t expected, uint64_t desired, uint64_t* old, int32_t device) {
+  if (!addr || !old) return fail(KVDP_EINVAL, "kvdp_flag_cas64: NULL argument");
+  if (((uintptr_t)addr & 7) != 0) return fail(KVDP_EALIGN, "kvdp_flag_cas64: address must be 8-byte aligned");
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lk(mu);
+  DeviceGuard g(device);
+  kvdp_cas64_kernel<<<1, 1>>>((unsigned long long*)addr, (unsigned long long)expected, (unsigned long long)desired);
+  KVDP_CUDA(cudaGetLastError());
+  unsigned long long found = 0;
+  KVDP_CUDA(cudaMemcpyFromSymbol(&found, g_cas_old, sizeof found));  // legacy default stream: ordered after the kernel
+  *old = (uint64_t)found;
   return 0;
 }
 

@@ -201,6 +201,13 @@ int kvdp_stream_synchronize(kvdp_stream_t stream);
 /* Make `stream` wait until *flag >= value (receiver side of kvdp_xfer_signal). */
 int kvdp_stream_wait_flag(kvdp_stream_t stream, uint32_t* flag, uint32_t value);
 
+/* System-scope compare-and-swap on one 8-byte-aligned 64-bit word of device memory (local, peer-mapped or IPC-mapped),
+ * executed by a one-thread kernel on `device`; *old receives the value that was found (the swap happened iff
+ * *old == expected). Synchronous. The connector's senders claim their notification lane in a receiver's mailbox with it:
+ * the counterpart of NIXL keeping one notification queue per remote agent (patch:1406-1425, nixl_wrapper.get_new_notifs
+ * returns {agent_name: [...]}). */
+int kvdp_flag_cas64(uint64_t* addr, uint64_t expected, uint64_t desired, uint64_t* old, int32_t device);
+
 /* ---- peers (replaces nixl_agent.register_memory / add_remote_agent metadata exchange, patch:1158-1186,1427-1436) */
 #define KVDP_IPC_HANDLE_BYTES 64
 int kvdp_peer_enable(int32_t device, int32_t peer_device);            /* same-process peers */

@@ -70,13 +70,13 @@ def test_write_blocks_reshards_and_notifies(gpu, ptp, dtp):
             assert np.array_equal(got[l][:, remote[:4]], want), (q, l)
         senders = sorted(p for p in range(ptp) if q in tp_targets(ptp, dtp, p))
         notifs = dec[q].get_new_notifs()
-        assert notifs == {str(p): [f"req-42-from-{p}"] for p in senders}
+        assert notifs == {f"prefill:{p}": [f"req-42-from-{p}"] for p in senders}
         assert dec[q].get_new_notifs() == {}
     # empty transfer: notify only (patch:1373-1377)
     pre[0].write_blocks([], [], [1, 2], "decode", "empty")
     pre[0].sync()
     for q in tp_targets(ptp, dtp, 0):
-        assert dec[q].get_new_notifs() == {"0": ["empty"]}
+        assert dec[q].get_new_notifs() == {"prefill:0": ["empty"]}
     for c in pre + dec:
         c.shutdown()
 
@@ -107,7 +107,7 @@ def test_write_token_rows_reshards_per_token(gpu, ptp, dtp):
             want[:, dst_slots] = flat_canon[l][:, src_slots][:, :, q * hq:(q + 1) * hq, :]
             assert np.array_equal(got[l].reshape(2, ND * BS, hq, D), want), (q, l)
         senders = sorted(p for p in range(ptp) if q in tp_targets(ptp, dtp, p))
-        assert dec[q].get_new_notifs() == {str(p): [f"tok-{p}"] for p in senders}
+        assert dec[q].get_new_notifs() == {f"prefill:{p}": [f"tok-{p}"] for p in senders}
     with pytest.raises(KvError):
         pre[0].write_token_rows([0, 1], [0], "decode", "bad")
     for c in pre + dec:
@@ -164,7 +164,7 @@ def test_mla_latent_cache_is_replicated(gpu):
         for l in range(L):
             got = dbufs[r][l].download().reshape(nb, bs, hd)
             assert np.array_equal(got[[0, 3]], src_h[l][[5, 1]])
-        assert decs[r].get_new_notifs() == {"0": ["mla"]}
+        assert decs[r].get_new_notifs() == {"p:0": ["mla"]}
     for c in [pre] + decs:
         c.shutdown()
 
@@ -179,11 +179,92 @@ def test_many_notifications_wrap_the_mailbox_ring(gpu):
         sent.append(f"r{k}")
         if k % 40 == 39:
             pre[0].sync()
-            got = dec[0].get_new_notifs().get("0", [])
+            got = dec[0].get_new_notifs().get("prefill:0", [])
             assert got == sent[:len(got)]
             sent = sent[len(got):]
     pre[0].sync()
-    assert dec[0].get_new_notifs().get("0", []) == sent
+    assert dec[0].get_new_notifs().get("prefill:0", []) == sent
+    for c in pre + dec:
+        c.shutdown()
+    del dec_bufs, pre_bufs
+
+
+def test_two_prefill_engines_with_equal_ranks_feed_one_decode_engine(gpu):
+    """Two senders whose rank numbers coincide must not share a notification lane or a ring slot (NIXL keeps one queue
+    per remote agent). Interleaved writes from both; every message arrives once, under its sender's agent name."""
+    rng = np.random.Generator(np.random.PCG64(77))
+    canon_a = rng.integers(0, 2 ** 15, size=(L, 2, NP, BS, H, D), dtype=np.int16)
+    canon_b = rng.integers(0, 2 ** 15, size=(L, 2, NP, BS, H, D), dtype=np.int16)
+    dec, dec_bufs, dec_meta = make_engine(gpu, "decode", 1, ND)
+    pa, pa_bufs, _ = make_engine(gpu, "prefill-a", 1, NP, canon_a)
+    pb, pb_bufs, _ = make_engine(gpu, "prefill-b", 1, NP, canon_b)
+    for c in pa + pb:
+        c.add_remote_agent("decode", dec_meta.agent_metadata, 1, None, ND)
+    assert pa[0]._remotes["decode"].lane[0] != pb[0]._remotes["decode"].lane[0]
+    sent_a, sent_b = [], []
+    for k in range(30):
+        pa[0].write_blocks([k % NP], [0], [k % 5], "decode", f"a{k}")
+        sent_a.append(f"a{k}")
+        if k % 3 == 0:
+            pb[0].write_blocks([k % NP], [0], [5 + k % 5], "decode", f"b{k}")
+            sent_b.append(f"b{k}")
+    pa[0].sync()
+    pb[0].sync()
+    assert dec[0].get_new_notifs() == {"prefill-a:0": sent_a, "prefill-b:0": sent_b}
+    got = read_rank(dec_bufs, 0, 1, ND)
+    for l in range(L):
+        assert np.array_equal(got[l][:, 4], canon_a[l][:, 29 % NP])        # last writer of decode block 4 was a29
+        assert np.array_equal(got[l][:, 5 + 27 % 5], canon_b[l][:, 27 % NP])
+    # the decode engine can tell where each sender's counter lives (what a stream-wait needs)
+    assert dec[0].notif_head_ptr("prefill-a:0") != dec[0].notif_head_ptr("prefill-b:0") != 0
+    assert dec[0].notif_head_ptr("nobody:0") == 0
+    for c in pa + pb + dec:
+        c.shutdown()
+    del dec_bufs, pa_bufs, pb_bufs
+
+
+def test_one_prefill_engine_feeds_two_decode_engines(gpu):
+    """The sender's pinned staging ring is shared by all its peers: alternating targets must not let one peer's message
+    land in the other's mailbox, also when the ring wraps (more than 64 messages in flight over the session)."""
+    rng = np.random.Generator(np.random.PCG64(78))
+    canon = rng.integers(0, 2 ** 15, size=(L, 2, NP, BS, H, D), dtype=np.int16)
+    pre, pre_bufs, _ = make_engine(gpu, "prefill", 1, NP, canon)
+    d1, d1_bufs, m1 = make_engine(gpu, "decode-1", 1, ND)
+    d2, d2_bufs, m2 = make_engine(gpu, "decode-2", 1, ND)
+    pre[0].add_remote_agent("decode-1", m1.agent_metadata, 1, None, ND)
+    pre[0].add_remote_agent("decode-2", m2.agent_metadata, 1, None, ND)
+    want1, want2 = [], []
+    for k in range(100):
+        eng, want = ("decode-1", want1) if k % 2 == 0 else ("decode-2", want2)
+        pre[0].write_blocks([k % NP], [0], [k % ND], eng, f"{eng}/r{k}")
+        want.append(f"{eng}/r{k}")
+        if k == 59:                        # both rings hold 30 unread messages here; drain like a polling worker would
+            pre[0].sync()
+            assert d1[0].get_new_notifs() == {"prefill:0": want1}
+            assert d2[0].get_new_notifs() == {"prefill:0": want2}
+            want1, want2 = [], []
+    pre[0].sync()
+    assert d1[0].get_new_notifs() == {"prefill:0": want1}
+    assert d2[0].get_new_notifs() == {"prefill:0": want2}
+    assert sorted(pre[0].get_done_tranfers()) == sorted(f"decode-{1 + k % 2}/r{k}" for k in range(100))
+    for c in pre + d1 + d2:
+        c.shutdown()
+    del pre_bufs, d1_bufs, d2_bufs
+
+
+def test_sender_waits_for_the_receiver_instead_of_overwriting_unread_notifications(gpu):
+    dec, dec_bufs, dec_meta = make_engine(gpu, "decode", 1, ND)
+    pre, pre_bufs, _ = make_engine(gpu, "prefill", 1, NP)
+    pre[0].add_remote_agent("decode", dec_meta.agent_metadata, 1, None, ND)
+    pre[0].notify_timeout_s = 0.2
+    for k in range(64):
+        pre[0].write_blocks([], [], [], "decode", f"n{k}")
+    with pytest.raises(KvError, match="unread notifications"):
+        pre[0].write_blocks([], [], [], "decode", "one too many")
+    assert dec[0].get_new_notifs() == {"prefill:0": [f"n{k}" for k in range(64)]}
+    pre[0].write_blocks([], [], [], "decode", "fits again")
+    pre[0].sync()
+    assert dec[0].get_new_notifs() == {"prefill:0": ["fits again"]}
     for c in pre + dec:
         c.shutdown()
     del dec_bufs, pre_bufs
