@@ -67,6 +67,7 @@ def parse_args():
                     help="N>1: push = prefill-side kernel stores into the decode GPU; pull = decode-side kernel loads "
                          "from the prefill GPU; both = measure both, headline the faster")
     ap.add_argument("--no-comparators", action="store_true", help="N>1: skip the NCCL / memcpy-peer comparison legs")
+    ap.add_argument("--no-reshard", action="store_true", help="N>1: skip the Llama-3-70B TP reshard legs (config 3)")
     ap.add_argument("--sweep", action="store_true", help="print a table of kernel variants instead of the JSON line")
     return ap.parse_args()
 
@@ -206,26 +207,42 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ CPU legs (oracle)
-def cpu_relayout_leg(threads: int, min_seconds: float, blocks: int = BLOCKS_PER_REQ):
-    """The reference's host block-copy loop restated in C (oracle/layout_oracle.c), on `blocks` Llama-3-8B blocks."""
-    from oracle import kvoracle as ko
-    ko.lib()
-    n_src = blocks
-    layers = [np.empty(2 * n_src * CHUNK, dtype=np.uint8) for _ in range(L8B)]
-    for i, a in enumerate(layers):
-        a[:] = (i * 7 + 1) & 0xFF  # touch every page
-    contig = np.zeros(blocks * BLOCK_BYTES, dtype=np.uint8)
-    rng = np.random.Generator(np.random.PCG64(1234))
-    sid, did = rng.permutation(n_src).astype(np.int32), rng.permutation(blocks).astype(np.int32)
-    ko.relayout_contig(layers, 0, n_src, CHUNK, contig, sid, did, True, threads)  # warm-up
-    reps, t0 = 0, time.perf_counter()
+class CpuRelayout:
+    """The reference's host block-copy loop restated in C (oracle/layout_oracle.c): layer-separate -> contiguous-per-block
+    relayout of Llama-3-8B blocks by memcpy on the host cores. `cache_blocks` blocks live in each cache; a step moves
+    `blocks` of them, a different window every step, exactly like the GPU arm's step."""
+
+    def __init__(self, blocks: int, cache_blocks: int):
+        from oracle import kvoracle as ko
+        ko.lib()
+        self.ko, self.blocks, self.n = ko, blocks, max(cache_blocks, blocks)
+        self.layers = [np.empty(2 * self.n * CHUNK, dtype=np.uint8) for _ in range(L8B)]
+        for i, a in enumerate(self.layers):
+            a[:] = (i * 7 + 1) & 0xFF  # touch every page
+        self.contig = np.zeros(self.n * BLOCK_BYTES, dtype=np.uint8)
+        rng = np.random.Generator(np.random.PCG64(1234))
+        self.sperm, self.dperm = rng.permutation(self.n).astype(np.int32), rng.permutation(self.n).astype(np.int32)
+
+    def step(self, k: int, threads: int) -> float:
+        w = max(1, self.n // self.blocks)
+        o = (k % w) * self.blocks
+        t0 = time.perf_counter()
+        self.ko.relayout_contig(self.layers, 0, self.n, CHUNK, self.contig, self.sperm[o:o + self.blocks],
+                                self.dperm[o:o + self.blocks], True, threads)
+        return time.perf_counter() - t0
+
+
+def cpu_relayout_leg(threads: int, min_seconds: float, blocks: int = BLOCKS_PER_REQ, cache_blocks: int = 0, leg=None):
+    """GB/s of payload and seconds per step of the CPU relayout, repeated for at least `min_seconds`."""
+    leg = leg or CpuRelayout(blocks, cache_blocks or blocks)
+    leg.step(0, threads)  # warm-up
+    reps, spent = 0, 0.0
     while True:
-        ko.relayout_contig(layers, 0, n_src, CHUNK, contig, sid, did, True, threads)
+        spent += leg.step(reps + 1, threads)
         reps += 1
-        dt = time.perf_counter() - t0
-        if dt >= min_seconds:
+        if spent >= min_seconds:
             break
-    return blocks * BLOCK_BYTES * reps / dt / GB, dt / reps
+    return leg.blocks * BLOCK_BYTES * reps / spent / GB, spent / reps
 
 
 def cpu_hash_leg(threads: int, min_seconds: float):
@@ -249,33 +266,37 @@ def cpu_hash_leg(threads: int, min_seconds: float):
 
 
 def run_reference(args):
-    """--impl reference: the CPU implementation of the path on the host cores, same metric/unit/config."""
+    """--impl reference: the CPU implementation of the path on the host cores, same metric / unit / config / step."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import kvoracle as ko
     threads = ko.hw_threads()
-    for _ in range(args.warmup):
-        cpu_relayout_leg(threads, 0.0)
-    vals = []
+    blocks = BLOCKS_PER_REQ * args.requests
+    # same step as the GPU arm: `blocks` blocks out of caches of `cache_blocks`; the cache is capped at 2 steps' worth
+    # so that the host allocation stays at 2 x 8 GiB
+    leg = CpuRelayout(blocks, min(args.cache_blocks, 2 * blocks))
+    for k in range(args.warmup):
+        leg.step(k, threads)
+    secs = []
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        v, _ = cpu_relayout_leg(threads, 0.0)
-        vals.append(v)
+    for k in range(args.steps):
+        secs.append(leg.step(args.warmup + k, threads))
         if time.perf_counter() - t0 > 150:
             break
-    # one step = one bounded sample (one 64-block request: 512 MiB read + 512 MiB written by memcpy)
-    value = float(np.mean(vals))
-    step_s = BLOCKS_PER_REQ * BLOCK_BYTES / (value * GB)
+    step_s = float(np.mean(secs))
+    value = blocks * BLOCK_BYTES / step_s / GB
+    del leg
     hps = cpu_hash_leg(threads, 2.0)
     line = {
         "impl": "reference", "metric": "kv_transfer_GBps", "value": value, "unit": "GB/s", "n_gpus": args.gpus,
-        "steps": len(vals), "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
+        "steps": len(secs), "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": workload_config(args, sample=True),
+        "config": workload_config(args),
         "cpu_baseline": {"value": value, "unit": "GB/s", "cores": threads, "kind": "port",
-                         "sample": "one 64-block Llama-3-8B request (512 MiB payload) per step, layer-separate -> "
-                                   "contiguous relayout by memcpy (oracle/layout_oracle.c), all host threads"},
+                         "sample": "%d Llama-3-8B blocks (%d MiB payload) per step, layer-separate -> contiguous relayout "
+                                   "by memcpy (oracle/layout_oracle.c), all host threads; host-resident caches of %d "
+                                   "blocks" % (blocks, blocks * BLOCK_BYTES >> 20, min(args.cache_blocks, 2 * blocks))},
         "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "blocks_per_s": value * GB / BLOCK_BYTES,
         "hash": {"hashes_per_s": hps, "cores": threads, "kind": "port"},
@@ -284,13 +305,13 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, sample=False):
+def workload_config(args):
     return {
         "workload": "llama3-8b-shape KV blocks (32 layers, 8 KV heads x 128, 64-token blocks, bf16 = 8 MiB/block), "
                     "ISL 4k requests (64 blocks), layer-separate -> contiguous-per-block"
                     + (" + NVLink peer push prefill->decode" if args.gpus > 1 else " relayout on one GPU"),
-        "requests_per_step": 1 if sample else args.requests,
-        "blocks_per_step": BLOCKS_PER_REQ * (1 if sample else args.requests),
+        "requests_per_step": args.requests,
+        "blocks_per_step": BLOCKS_PER_REQ * args.requests,
         "cache_blocks": args.cache_blocks,
         "l2_policy": "inputs larger than L2: every step reads/writes a different %d MiB window of 8 GiB caches"
                      % (BLOCKS_PER_REQ * args.requests * BLOCK_BYTES >> 20),

@@ -19,8 +19,19 @@ import numpy as np
 from bench import BLOCK_BYTES, BLOCKS_PER_REQ, CHUNK, GB, L8B, ClockSampler, env_info, workload_config
 from bench_single import Setup
 
-NVLINK_PEAK_MEASURED = 770.0   # GB/s per direction per GPU, peer copy (B200_PROFILING.md)
+NVLINK_PEAK_FALLBACK = 770.0   # GB/s per direction per GPU, peer copy (B200_PROFILING.md); used only when the in-run
+                               # cudaMemcpyAsync-to-peer comparator is skipped (--no-comparators)
 NVLINK_PEAK_NOMINAL = 900.0
+
+
+def synth_words(torch, seed: int, nbytes: int):
+    """`nbytes` (a multiple of 8) of synthetic payload as int64 words: a closed-form mix of (seed, word index), so the
+    GPU that receives a transfer can regenerate what its peer holds and compare every byte."""
+    x = torch.arange(nbytes // 8, dtype=torch.int64, device="cuda")
+    x = x * 0x9E3779B97F4A7C1 + (((seed + 1) * 0x2545F4914F6CDD1D) & 0x7FFFFFFFFFFFFFFF)      # wraps mod 2^64
+    x = x ^ (x >> 29)
+    x = x * (0x94D049BB133111EB - (1 << 64))
+    return x ^ (x >> 32)
 
 
 class CudaArray:
@@ -68,13 +79,15 @@ def run_multi(args, rank, local_rank, world):
     lib.check(L.kvdp_device_alloc(C.byref(flag_ptr), 256, local_rank))
     handles = {"flag": export(flag_ptr)}
     own_layers, own_cache = [], C.c_void_p()
+    def layer_seed(prefill_rank, l):
+        return 1000 * (prefill_rank + 1) + l
+
     if is_prefill:
-        g = torch.Generator(device="cuda")
-        g.manual_seed(42 + rank)
-        for _ in range(L8B):
+        for l in range(L8B):
             p = C.c_void_p()
             lib.check(L.kvdp_device_alloc(C.byref(p), 2 * n * CHUNK, local_rank))
-            torch.as_tensor(CudaArray(p.value, 2 * n * CHUNK), device="cuda").random_(0, 256, generator=g)
+            torch.as_tensor(CudaArray(p.value, 2 * n * CHUNK), device="cuda").view(torch.int64).copy_(
+                synth_words(torch, layer_seed(rank, l), 2 * n * CHUNK))
             own_layers.append(p)
         handles["layers"] = [export(p) for p in own_layers]
     else:
@@ -120,38 +133,27 @@ def run_multi(args, rank, local_rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    def verify(mode, step, samples=4):
-        """Runner announces sampled (src id, dst id, layer, kv); prefill ships the source chunk; decode compares."""
-        runner = is_prefill if mode == "push" else not is_prefill
-        ok = torch.ones(1, dtype=torch.int32, device="cuda")
-        meta = torch.zeros(samples * 4, dtype=torch.int64, device="cuda")
-        if runner:
-            s_ids, d_ids = setup.ids(step)
-            rng = np.random.Generator(np.random.PCG64(step))
-            rows = []
-            for _ in range(samples):
-                i = int(rng.integers(pairs))
-                rows += [int(s_ids[i]), int(d_ids[i]), int(rng.integers(L8B)), int(rng.integers(2))]
-            meta = torch.tensor(rows, dtype=torch.int64, device="cuda")
-            dist.send(meta, partner)
-        else:
-            dist.recv(meta, partner)
-        rows = meta.tolist()
-        for j in range(samples):
-            s, d, l, kv = rows[4 * j:4 * j + 4]
-            if is_prefill:
-                layer = torch.as_tensor(CudaArray(own_layers[l].value, 2 * n * CHUNK), device="cuda")
-                dist.send(layer[(kv * n + s) * CHUNK:(kv * n + s + 1) * CHUNK].contiguous(), partner)
-            else:
-                buf = torch.empty(CHUNK, dtype=torch.uint8, device="cuda")
-                dist.recv(buf, partner)
-                cache = torch.as_tensor(CudaArray(own_cache.value, n * BLOCK_BYTES), device="cuda")
-                off = d * BLOCK_BYTES + (l * 2 + kv) * CHUNK
-                if not torch.equal(buf, cache[off:off + CHUNK]):
-                    ok.zero_()
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        if int(ok.item()) != 1:
-            raise RuntimeError("%s result differs from its source" % mode)
+    def verify(mode, step):
+        """Every byte of the step's blocks: the decode rank regenerates its partner's layers from their seeds and compares
+        all 32 layers x K|V of every (source id -> destination id) pair with what the transfer left in its cache."""
+        bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+        if not is_prefill:
+            rng_p = np.random.Generator(np.random.PCG64(1234 + (rank if mode == "pull" else partner)))
+            sperm = rng_p.permutation(n).astype(np.int32)
+            dperm = rng_p.permutation(n).astype(np.int32)
+            w = max(1, n // pairs)
+            o = (step % w) * pairs
+            s_t = torch.from_numpy(sperm[o:o + pairs].astype(np.int64)).cuda()
+            d_t = torch.from_numpy(dperm[o:o + pairs].astype(np.int64)).cuda()
+            cache = torch.as_tensor(CudaArray(own_cache.value, n * BLOCK_BYTES), device="cuda").view(torch.int64)
+            cache = cache.view(n, L8B, 2, CHUNK // 8)
+            for l in range(L8B):
+                src = synth_words(torch, layer_seed(partner, l), 2 * n * CHUNK).view(2, n, CHUNK // 8)
+                bad += (src[:, s_t].transpose(0, 1) != cache[d_t, l]).sum()
+        dist.all_reduce(bad, op=dist.ReduceOp.SUM)
+        if int(bad.item()) != 0:
+            raise RuntimeError("%s: %d 8-byte words differ from their source" % (mode, int(bad.item())))
+        return P * pairs * BLOCK_BYTES
 
     modes = ["push", "pull"] if args.mode == "both" else [args.mode]
     results, clk = {}, None
@@ -164,9 +166,10 @@ def run_multi(args, rank, local_rank, world):
         sec = timed(mode, warmup, steps)
         c = clocks.stop()
         clk = clk or c
-        verify(mode, warmup + steps - 1)
+        verified = verify(mode, warmup + steps - 1)
         results[mode] = {"value": P * pairs * BLOCK_BYTES * steps / sec / GB, "sec": sec,
-                         "per_direction": pairs * BLOCK_BYTES * steps / sec / GB * max(1, P // D)}
+                         "per_direction": pairs * BLOCK_BYTES * steps / sec / GB * max(1, P // D),
+                         "verified_bytes_last_step": verified}
 
     # ---- e2e: source blocks in pinned HOST memory on the prefill side, ONE kernel reads them over PCIe and stores
     # them into the decode GPU's cache over NVLink (no bounce through prefill HBM); decode reads back 8 bytes.
@@ -238,37 +241,21 @@ def run_multi(args, rank, local_rank, world):
             t = torch.tensor([a.elapsed_time(b) / 1e3], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             return float(t.item())
-        def token_verify(mode, samples=6):
-            """The runner announces sampled (src slot, dst slot, layer, kv); prefill ships the source row over NCCL;
-            decode compares it with what the transfer left in its cache."""
-            runner = is_prefill if mode == "push" else not is_prefill
-            okf = torch.ones(1, dtype=torch.int32, device="cuda")
-            meta = torch.zeros(samples * 4, dtype=torch.int64, device="cuda")
-            if runner:
-                pick = np.random.Generator(np.random.PCG64(5)).integers(0, ntok, size=samples)
-                rows_ = []
-                for j, i in enumerate(pick):
-                    rows_ += [int(ts_ids[i]), int(td_ids[i]), (7 * j) % L8B, j % 2]
-                meta = torch.tensor(rows_, dtype=torch.int64, device="cuda")
-                dist.send(meta, partner)
-            else:
-                dist.recv(meta, partner)
-            rows_ = meta.tolist()
-            for j in range(samples):
-                ss, dd, l, kv = rows_[4 * j:4 * j + 4]
-                if is_prefill:
-                    layer = torch.as_tensor(CudaArray(own_layers[l].value, layer_bytes), device="cuda")
-                    dist.send(layer[(kv * slots + ss) * row:(kv * slots + ss + 1) * row].contiguous(), partner)
-                else:
-                    buf = torch.empty(row, dtype=torch.uint8, device="cuda")
-                    dist.recv(buf, partner)
-                    cache = torch.as_tensor(CudaArray(own_cache.value, n * BLOCK_BYTES), device="cuda")
-                    off = l * layer_bytes + (kv * slots + dd) * row
-                    if not torch.equal(buf, cache[off:off + row]):
-                        okf.zero_()
-            dist.all_reduce(okf, op=dist.ReduceOp.MIN)
-            if int(okf.item()) != 1:
-                raise RuntimeError("token-granular %s result differs from its source" % mode)
+        def token_verify(mode):
+            """Every transferred row of every layer, K and V, against the regenerated source."""
+            bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+            if not is_prefill:
+                rng_v = np.random.Generator(np.random.PCG64(99 + rank))
+                s_t = torch.from_numpy(rng_v.permutation(slots)[:ntok].astype(np.int64)).cuda()
+                d_t = torch.from_numpy(rng_v.permutation(slots)[:ntok].astype(np.int64)).cuda()
+                cache = torch.as_tensor(CudaArray(own_cache.value, n * BLOCK_BYTES), device="cuda").view(torch.int64)
+                cache = cache.view(L8B, 2, slots, row // 8)
+                for l in range(L8B):
+                    src = synth_words(torch, layer_seed(partner, l), layer_bytes).view(2, slots, row // 8)
+                    bad += (src[:, s_t] != cache[l][:, d_t]).sum()
+            dist.all_reduce(bad, op=dist.ReduceOp.SUM)
+            if int(bad.item()) != 0:
+                raise RuntimeError("token-granular %s: %d words differ from their source" % (mode, int(bad.item())))
 
         token = {"tokens_per_launch": ntok, "run_bytes": row, "runs_per_launch": ntok * 2 * L8B}
         k_t = max(2, min(steps, 10))
@@ -337,33 +324,49 @@ def run_multi(args, rank, local_rank, world):
         memcpy_steps()
         memcpy_value = P * pairs * BLOCK_BYTES * nsteps_c / timed_default_stream(memcpy_steps) / GB
 
+    # ---- BASELINE config 3: Llama-3-70B-shaped TP-P -> TP-D head resharding through the connector (bench_reshard.py)
+    reshard = []
+    if not getattr(args, "no_reshard", False):
+        from bench_reshard import configs_for, reshard_leg
+        for p_tp, d_tp in configs_for(world):
+            res = reshard_leg(torch, dist, lib, rank, local_rank, world, p_tp, d_tp, steps, warmup,
+                              clock_sampler=ClockSampler(local_rank))
+            if rank == 0:
+                reshard.append(res)
+
     if rank == 0:
         best = max(results, key=lambda m: results[m]["value"])
         r = results[best]
         cfg = workload_config(args)
-        cfg["pairs"] = ["%d->%d" % (a, b) for a, b in role_pairs]
-        cfg["pairing"] = args.pairing
-        cfg["mode"] = best
+        topo = {"pairs": ["%d->%d" % (a, b) for a, b in role_pairs], "pairing": args.pairing, "mode": best}
+        # the link's practical ceiling is what the copy engine reaches on the same payload in this very run
+        peak = memcpy_value / P * max(1, P // D) if memcpy_value else NVLINK_PEAK_FALLBACK
+        peak_src = ("cudaMemcpyAsync to the peer measured in this run, per direction per GPU" if memcpy_value else
+                    "fallback: peer copy per direction per GPU (B200_PROFILING.md)")
+        launches = steps * len(modes) + sum(x["steps"] * 2 for x in reshard)
         line = {
             "metric": "kv_transfer_GBps", "value": r["value"], "unit": "GB/s", "n_gpus": world, "steps": steps,
             "warmup": warmup, "ms_per_step": r["sec"] / steps * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg, "topology": topo,
             "blocks_per_s": P * pairs * steps / r["sec"],
             "modes": {m: {"value": v["value"], "per_direction_GBps": v["per_direction"],
                           "frac_of_nominal_900": v["per_direction"] / NVLINK_PEAK_NOMINAL,
-                          "frac_of_measured_770": v["per_direction"] / NVLINK_PEAK_MEASURED}
+                          "frac_of_peer_memcpy": v["per_direction"] / peak,
+                          "verified_bytes_last_step": v["verified_bytes_last_step"]}
                       for m, v in results.items()},
-            "roofline": {"bound": "nvlink", "achieved": r["per_direction"], "peak": NVLINK_PEAK_MEASURED,
-                         "unit": "GB/s", "frac": r["per_direction"] / NVLINK_PEAK_MEASURED, "traffic": None,
+            "verification": "all bytes: each decode GPU regenerates its partner's 32 layers and compares every block of "
+                            "the last timed step (and every row of the token-granular leg)",
+            "roofline": {"bound": "nvlink", "achieved": r["per_direction"], "peak": peak,
+                         "unit": "GB/s", "frac": r["per_direction"] / peak, "traffic": None,
                          "kernel": "kvdp_copy_tma_tma_kernel over peer-mapped memory (%s)" % best,
-                         "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
+                         "peak_source": peak_src + "; nominal 900",
                          "frac_of_nominal_900": r["per_direction"] / NVLINK_PEAK_NOMINAL,
-                         "note": "achieved = wire bytes per direction on the busiest port / time"},
+                         "note": "achieved = payload bytes per direction on the busiest port / time"},
             "comparators": {"nccl_send_recv_GBps": nccl_value, "cuda_memcpy_peer_GBps": memcpy_value,
                             "steps": nsteps_c},
             "options": {k: lib.get_option(k) for k in ("copy_path", "tile_bytes", "stages", "ctas_per_sm")},
-            "gpu_launches": steps * len(modes), "clocks": clk, "env": env_info(torch, local_rank),
-            "e2e": e2e, "token_transfer": token,
+            "gpu_launches": launches, "clocks": clk, "env": env_info(torch, local_rank),
+            "e2e": e2e, "token_transfer": token, "reshard": reshard,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()

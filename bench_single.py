@@ -135,84 +135,133 @@ def time_kernel_only(torch, lib, setup, launches, warmup=3):
 
 
 def e2e_legacy(torch, lib, args, steps, warmup):
-    """Reference-facing path: pinned layer-separate host blocks -> device through the legacy CopyStream C ABI
-    (copy_stream_prepare_block_ids + copy_stream_memcpy per layer + copy_stream_sync), then an 8-byte read-back."""
+    """Reference-facing path, a full trip with HOST buffers through the legacy CopyStream C ABI
+    (copy_stream_prepare_block_ids + copy_stream_memcpy per layer + copy_stream_sync, kv/layer.rs:785-979): every step
+    ONBOARDS one batch of blocks (pinned host layer-separate cache -> HBM cache) and OFFLOADS another batch of the same
+    size (HBM cache -> pinned host cache), each through its own CopyStream, as the reference's pool of CopyStreams
+    allows; the two directions share the PCIe link in opposite directions. value = payload of both batches / wall time.
+    Each direction is also timed alone against its own link ceiling."""
     L = lib.lib()
     pairs = BLOCKS_PER_REQ * args.requests
-    nh = pairs
-    nd = pairs
-    host_layers, host_ptrs = [], []
-    for l in range(L8B):
-        p = C.c_void_p()
-        lib.check(L.cuda_malloc_host(C.byref(p), 2 * nh * CHUNK))
-        a = np.frombuffer((C.c_uint8 * (2 * nh * CHUNK)).from_address(p.value), dtype=np.uint8)
-        a[:] = (l * 13 + 5) & 0xFF
-        a[::4096] = np.arange(a[::4096].size, dtype=np.uint64).astype(np.uint8)
-        host_layers.append(a)
-        host_ptrs.append(p.value)
-    dev_layers = [torch.zeros(2 * nd * CHUNK, dtype=torch.uint8, device="cuda") for _ in range(L8B)]
-    cs = C.c_void_p()
-    assert L.copy_stream_create(C.byref(cs), L8B, pairs) == 0
+    nh = nd = pairs
+    layer_bytes = 2 * nh * CHUNK
+
+    def pinned_layers(fill):
+        arrs, ptrs = [], []
+        for l in range(L8B):
+            p = C.c_void_p()
+            lib.check(L.cuda_malloc_host(C.byref(p), layer_bytes))
+            a = np.frombuffer((C.c_uint8 * layer_bytes).from_address(p.value), dtype=np.uint8)
+            if fill:
+                w = a.view(np.uint64)
+                w[:] = np.arange(w.size, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15) + np.uint64(l)
+            else:
+                a[:] = 0
+            arrs.append(a)
+            ptrs.append(p.value)
+        return arrs, ptrs
+    host_in, host_in_p = pinned_layers(True)            # onboard source
+    host_out, host_out_p = pinned_layers(False)         # offload destination
+    dev_in = [torch.zeros(layer_bytes, dtype=torch.uint8, device="cuda") for _ in range(L8B)]
+    g = torch.Generator(device="cuda")
+    g.manual_seed(4242)
+    dev_out = [torch.empty(layer_bytes, dtype=torch.uint8, device="cuda").random_(0, 256, generator=g)
+               for _ in range(L8B)]
+    cs_on, cs_off = C.c_void_p(), C.c_void_p()
+    assert L.copy_stream_create(C.byref(cs_on), L8B, pairs) == 0
+    assert L.copy_stream_create(C.byref(cs_off), L8B, pairs) == 0
     rng = np.random.Generator(np.random.PCG64(77))
-    result = np.zeros(8, dtype=np.uint8)
-    t_total, timed = 0.0, 0
-    for k in range(steps + warmup):
-        sid, did = rng.permutation(nh).astype(np.int32), rng.permutation(nd).astype(np.int32)
+    suffix = BS * H8B * D8B
+
+    def one_step(onboard=True, offload=True):
+        ids = [rng.permutation(nh).astype(np.int32) for _ in range(4)]
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        lib.check(L.copy_stream_prepare_block_ids(cs, sid.ctypes.data, did.ctypes.data, pairs))
+        if onboard:
+            lib.check(L.copy_stream_prepare_block_ids(cs_on, ids[0].ctypes.data, ids[1].ctypes.data, pairs))
+        if offload:
+            lib.check(L.copy_stream_prepare_block_ids(cs_off, ids[2].ctypes.data, ids[3].ctypes.data, pairs))
         for l in range(L8B):
-            lib.check(L.copy_stream_memcpy(cs, host_ptrs[l], dev_layers[l].data_ptr(), 2, BS * H8B * D8B, ELEM, nh, nd))
-        lib.check(L.copy_stream_sync(cs))
-        lib.check(L.cuda_memcpy_sync(result.ctypes.data, dev_layers[L8B - 1].data_ptr() + int(did[-1]) * CHUNK, 8))
-        dt = time.perf_counter() - t0
+            if onboard:
+                lib.check(L.copy_stream_memcpy(cs_on, host_in_p[l], dev_in[l].data_ptr(), 2, suffix, ELEM, nh, nd))
+            if offload:
+                lib.check(L.copy_stream_memcpy(cs_off, dev_out[l].data_ptr(), host_out_p[l], 2, suffix, ELEM, nd, nh))
+        if onboard:
+            lib.check(L.copy_stream_sync(cs_on))
+        if offload:
+            lib.check(L.copy_stream_sync(cs_off))
+        return time.perf_counter() - t0, ids
+
+    t_total, timed, ids = 0.0, 0, None
+    for k in range(steps + warmup):
+        dt, ids = one_step()
         if k >= warmup:
             t_total += dt
             timed += 1
-        # result check: first 8 bytes of the last pair's K chunk in the last layer
-        want = host_layers[L8B - 1][int(sid[-1]) * CHUNK:int(sid[-1]) * CHUNK + 8]
-        if not np.array_equal(result, want):
-            raise RuntimeError("e2e result mismatch")
+    # every byte of the last step, both directions
+    for l in range(L8B):
+        want = torch.from_numpy(host_in[l]).view(2, nh, CHUNK)[:, torch.from_numpy(ids[0].astype(np.int64))].cuda()
+        if not torch.equal(dev_in[l].view(2, nd, CHUNK)[:, torch.from_numpy(ids[1].astype(np.int64)).cuda()], want):
+            raise RuntimeError("e2e onboard result differs from its source (layer %d)" % l)
+        got = torch.from_numpy(host_out[l]).view(2, nh, CHUNK)[:, torch.from_numpy(ids[3].astype(np.int64))].cuda()
+        if not torch.equal(dev_out[l].view(2, nd, CHUNK)[:, torch.from_numpy(ids[2].astype(np.int64)).cuda()], got):
+            raise RuntimeError("e2e offload result differs from its source (layer %d)" % l)
+    one_step(True, False)
+    t_on = min(one_step(True, False)[0] for _ in range(3))
+    one_step(False, True)
+    t_off = min(one_step(False, True)[0] for _ in range(3))
     # comparator: the same call sequence with the reference's data movement behind it, one cudaMemcpyAsync per
     # (K|V, pair) chunk (block_copy.cu:246-305), which libkvdp keeps as host_path = 1
     dma_loop = None
     if lib.get_option("host_path") == 0:
         lib.set_option("host_path", 1)
-        t_dma = 0.0
-        for k in range(2):
-            sid, did = rng.permutation(nh).astype(np.int32), rng.permutation(nd).astype(np.int32)
+        dma_loop = pairs * BLOCK_BYTES / min(one_step(True, False)[0] for _ in range(2)) / GB
+        lib.set_option("host_path", 0)
+    # practical ceilings of the host link on this box: contiguous 1 GiB pinned DMAs, each way alone and both at once
+    n_c = min(1 << 30, layer_bytes * 4)
+    big_h = C.c_void_p()
+    lib.check(L.cuda_malloc_host(C.byref(big_h), 2 * n_c))
+    big_d = torch.empty(2 * n_c, dtype=torch.uint8, device="cuda")
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def dma(h2d, d2h):
+        best = 0.0
+        for _ in range(3):
             torch.cuda.synchronize()
             t0 = time.perf_counter()
-            lib.check(L.copy_stream_prepare_block_ids(cs, sid.ctypes.data, did.ctypes.data, pairs))
-            for l in range(L8B):
-                lib.check(L.copy_stream_memcpy(cs, host_ptrs[l], dev_layers[l].data_ptr(), 2, BS * H8B * D8B, ELEM, nh, nd))
-            lib.check(L.copy_stream_sync(cs))
-            t_dma += time.perf_counter() - t0
-        lib.set_option("host_path", 0)
-        dma_loop = pairs * BLOCK_BYTES * 2 / t_dma / GB
-    # practical ceiling of the host link on this box: one contiguous 1 GiB pinned -> device DMA
-    n_c = min(1 << 30, 2 * nh * CHUNK)
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    best = 0.0
-    for _ in range(3):
-        a.record()
-        lib.check(L.cuda_memcpy_async(dev_layers[0].data_ptr(), host_ptrs[0], n_c, None))
-        b.record()
-        torch.cuda.synchronize()
-        best = max(best, n_c / (a.elapsed_time(b) / 1e3) / GB)
-    L.copy_stream_destroy(cs)
-    for p in host_ptrs:
+            if h2d:
+                lib.check(L.cuda_memcpy_async(big_d.data_ptr(), big_h.value, n_c, C.c_void_p(s1.cuda_stream)))
+            if d2h:
+                lib.check(L.cuda_memcpy_async(big_h.value + n_c, big_d.data_ptr() + n_c, n_c, C.c_void_p(s2.cuda_stream)))
+            torch.cuda.synchronize()
+            best = max(best, (int(h2d) + int(d2h)) * n_c / (time.perf_counter() - t0) / GB)
+        return best
+    ceil_h2d, ceil_d2h, ceil_both = dma(True, False), dma(False, True), dma(True, True)
+    L.cuda_free_host(big_h)
+    L.copy_stream_destroy(cs_on)
+    L.copy_stream_destroy(cs_off)
+    for p in host_in_p + host_out_p:
         L.cuda_free_host(C.c_void_p(p))
     sec = t_total / timed
-    return {"h2d_link_ceiling_GBps": best, "frac_of_link_ceiling": pairs * BLOCK_BYTES / sec / GB / best,
-            "host_path": "kernel zero-copy (SMs read pinned memory)" if lib.get_option("host_path") == 0
-            else "per-chunk cudaMemcpyAsync loop","value": pairs * BLOCK_BYTES / sec / GB, "unit": "GB/s", "h2d_bytes_per_step": pairs * BLOCK_BYTES,
-            "d2h_bytes_per_step": 8, "ms_per_step": sec * 1e3, "steps": timed,
+    payload = pairs * BLOCK_BYTES
+    return {"value": 2 * payload / sec / GB, "unit": "GB/s", "h2d_bytes_per_step": payload, "d2h_bytes_per_step": payload,
+            "ms_per_step": sec * 1e3, "steps": timed,
+            "step": "onboard %d blocks (pinned host -> HBM) + offload %d blocks (HBM -> pinned host), concurrently, "
+                    "each through its own legacy CopyStream" % (pairs, pairs),
+            "duplex_link_ceiling_GBps": ceil_both, "frac_of_duplex_link_ceiling": 2 * payload / sec / GB / ceil_both,
+            "onboard": {"GBps": payload / t_on / GB, "h2d_link_ceiling_GBps": ceil_h2d,
+                        "frac_of_link_ceiling": payload / t_on / GB / ceil_h2d},
+            "offload": {"GBps": payload / t_off / GB, "d2h_link_ceiling_GBps": ceil_d2h,
+                        "frac_of_link_ceiling": payload / t_off / GB / ceil_d2h},
+            "h2d_link_ceiling_GBps": ceil_h2d, "frac_of_link_ceiling": payload / t_on / GB / ceil_h2d,
+            "host_path": "kernel zero-copy (SMs read / write pinned memory)" if lib.get_option("host_path") == 0
+            else "per-chunk cudaMemcpyAsync loop",
+            "verification": "all bytes of the last step, both directions",
             "per_chunk_dma_loop_GBps": dma_loop,
-            "per_chunk_dma_loop_note": "same ABI calls with the reference's data movement (one cudaMemcpyAsync per chunk, "
-                                       "4096 per 64-block request) selected by kvdp_set_option(host_path, 1)",
-            "api": "legacy C ABI: copy_stream_prepare_block_ids + 32 x copy_stream_memcpy + copy_stream_sync "
-                   "(pinned host layer-separate blocks -> HBM), timed on the host clock around the blocking call"}
+            "per_chunk_dma_loop_note": "onboard alone with the reference's data movement behind the same ABI calls (one "
+                                       "cudaMemcpyAsync per chunk, 4096 per 64-block request): kvdp_set_option(host_path, 1)",
+            "api": "legacy C ABI: copy_stream_prepare_block_ids + 32 x copy_stream_memcpy + copy_stream_sync per "
+                   "direction, timed on the host clock around the blocking calls"}
 
 
 def host_tier_bench(torch, lib):
@@ -618,12 +667,17 @@ def run_single(args):
     if not args.no_cpu:
         from oracle import kvoracle as ko
         threads = ko.hw_threads()
-        v_all, _ = cpu_relayout_leg(threads, 6.0)
-        v_one, _ = cpu_relayout_leg(1, 3.0)
+        from bench import CpuRelayout
+        blocks = BLOCKS_PER_REQ * args.requests
+        leg = CpuRelayout(blocks, min(args.cache_blocks, 2 * blocks))
+        v_all, _ = cpu_relayout_leg(threads, 6.0, leg=leg)
+        v_one, _ = cpu_relayout_leg(1, 3.0, leg=leg)
+        del leg
         line["cpu_baseline"] = {
             "value": v_all, "unit": "GB/s", "cores": threads, "kind": "port",
-            "sample": "64 Llama-3-8B blocks (512 MiB payload) relaid out layer-separate -> contiguous by the C "
-                      "restatement of the reference's host copy loop (oracle/layout_oracle.c), repeated for >= 6 s",
+            "sample": "the bench step itself (%d Llama-3-8B blocks = %d MiB payload, layer-separate -> contiguous) done by "
+                      "the C restatement of the reference's host copy loop (oracle/layout_oracle.c) on host-resident "
+                      "caches, repeated for >= 6 s" % (blocks, blocks * BLOCK_BYTES >> 20),
             "single_thread_value": v_one,
             "hash_hashes_per_s": cpu_hash_leg(threads, 3.0), "hash_hashes_per_s_single_thread": cpu_hash_leg(1, 2.0)}
     print(json.dumps(line), flush=True)

@@ -33,6 +33,8 @@ struct Options {
   int64_t host_ctas = 0;    // CTAs used when one side is host memory (0 = default)
   int64_t l2_hint = 0;      // path 3: 1 = evict_first on loads, 2 = on stores, 3 = both
   int64_t vec32 = 0;        // path 1: 1 = 256-bit loads/stores when everything is 32-byte aligned
+  int64_t hash_stages = 0;  // chained hashing of a big batch: request ranges whose chains overlap the next range's
+                            // block hashing (0 = default 4, 1 = everything on the caller's stream)
 };
 Options& options();
 
@@ -42,6 +44,12 @@ struct DevInfo {
   int max_smem_optin = 0;
 };
 int device_info(int device, DevInfo* out);
+
+// token_hash.cu: kvdp_hash_token_blocks restricted to the caller's stream (no side streams are created or used)
+int hash_token_blocks_single_stream(const uint32_t* d_tokens, const int64_t* d_offsets, int64_t n_req,
+                                    int64_t total_tokens, int32_t block_size, uint64_t salt, int64_t* d_block_offsets,
+                                    uint64_t* d_block_hash, uint64_t* d_seq_hash, void* d_workspace,
+                                    size_t workspace_bytes, uint32_t flags, cudaStream_t stream);
 
 // the event publisher stops feeding an index that is about to be destroyed (event_capi.cu)
 void event_sink_forget_index(const void* index);

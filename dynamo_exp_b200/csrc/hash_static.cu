@@ -63,6 +63,8 @@ extern "C" int kvdp_hash_token_blocks_noalloc(const uint32_t* d_tokens, const in
   // Same kernels as the allocating-caller entry point; only the origin of the scratch differs. Nothing in the scratch
   // has to start at zero: every partial sum a call reads was written earlier in that same call, so whatever the
   // previous call left behind is never observed.
-  return kvdp_hash_token_blocks(d_tokens, d_offsets, n_req, total_tokens, block_size, salt, d_block_offsets,
-                                d_block_hash, d_seq_hash, scratch, kStaticScratchBytes, flags, stream);
+  // (the single-stream form: the side streams the allocating entry point may create on a big batch are not used here)
+  return kvdp::hash_token_blocks_single_stream(d_tokens, d_offsets, n_req, total_tokens, block_size, salt,
+                                               d_block_offsets, d_block_hash, d_seq_hash, scratch, kStaticScratchBytes,
+                                               flags, (cudaStream_t)stream);
 }

@@ -103,6 +103,9 @@ int kvdp_set_option(const char* name, int64_t value) {
   } else if (!strcmp(name, "vec32")) {
     if (value < 0 || value > 1) return fail(KVDP_EINVAL, "vec32 must be 0 or 1");
     o.vec32 = value;
+  } else if (!strcmp(name, "hash_stages")) {
+    if (value < 0 || value > 16) return fail(KVDP_EINVAL, "hash_stages must be 0..16");
+    o.hash_stages = value;
   } else if (!strcmp(name, "host_ctas")) {
     if (value < 0 || value > 4096) return fail(KVDP_EINVAL, "host_ctas out of range");
     o.host_ctas = value;
@@ -123,6 +126,7 @@ int64_t kvdp_get_option(const char* name) {
   if (!strcmp(name, "host_ctas")) return o.host_ctas;
   if (!strcmp(name, "l2_hint")) return o.l2_hint;
   if (!strcmp(name, "vec32")) return o.vec32;
+  if (!strcmp(name, "hash_stages")) return o.hash_stages;
   return -1;
 }
 

@@ -23,6 +23,7 @@
 
 #include <algorithm>
 #include <mutex>
+#include <vector>
 
 #include "common.cuh"
 
@@ -271,8 +272,10 @@ __global__ void __launch_bounds__(WARPS * 32) kvdp_hash_blocks_tma(const __grid_
   }
   __syncwarp();
 
-  const int64_t total = __ldg(A.block_offsets + A.n_req);
-  const int64_t tiles = (total + 31) >> 5;
+  // A launch covers the blocks of requests [0, n_req) of the (possibly shifted) offset arrays: global block indices
+  // [b_begin, total). For a whole batch b_begin is 0; a staged call passes arrays shifted to its first request.
+  const int64_t b_begin = __ldg(A.block_offsets), total = __ldg(A.block_offsets + A.n_req);
+  const int64_t tiles = (total - b_begin + 31) >> 5;
   // Each warp owns a CONTIGUOUS range of tiles: one binary search for its first block, then the request index only
   // walks forward (a per-tile binary search over 10^4..10^6 requests cost ~40% of the kernel's time).
   const int64_t warps_total = (int64_t)gridDim.x * WARPS;
@@ -282,19 +285,20 @@ __global__ void __launch_bounds__(WARPS * 32) kvdp_hash_blocks_tma(const __grid_
   int64_t r_tile = -1;  // request holding the first block of the tile being issued (warp-uniform)
   // Start the copies of tile t: every lane arrives once on the warp's barrier, through its copy's byte count or directly.
   auto issue = [&](int64_t t) {
-    const int64_t gb = t * 32 + lane;
+    const int64_t g0 = b_begin + t * 32;  // first block of the tile
+    const int64_t gb = g0 + lane;
     if (r_tile < 0) {
-      int64_t lo = 0, hi = A.n_req;  // invariant: block_offsets[lo] <= t*32 < block_offsets[hi]
+      int64_t lo = 0, hi = A.n_req;  // invariant: block_offsets[lo] <= g0 < block_offsets[hi]
       while (hi - lo > 1) {
         const int64_t mid = (lo + hi) >> 1;
-        if (__ldg(A.block_offsets + mid) <= t * 32)
+        if (__ldg(A.block_offsets + mid) <= g0)
           lo = mid;
         else
           hi = mid;
       }
       r_tile = lo;
     }
-    while (r_tile + 1 < A.n_req && __ldg(A.block_offsets + r_tile + 1) <= t * 32) ++r_tile;
+    while (r_tile + 1 < A.n_req && __ldg(A.block_offsets + r_tile + 1) <= g0) ++r_tile;
     if (gb < total) {
       int64_t r = r_tile;
       while (r + 1 < A.n_req && __ldg(A.block_offsets + r + 1) <= gb) ++r;
@@ -316,7 +320,7 @@ __global__ void __launch_bounds__(WARPS * 32) kvdp_hash_blocks_tma(const __grid_
   uint32_t parity = 0;
   if (t_begin < t_end) issue(t_begin);
   for (int64_t t = t_begin; t < t_end; ++t) {
-    const int64_t gb = t * 32 + lane;
+    const int64_t gb = b_begin + t * 32 + lane;
     const bool valid = gb < total;
     mbar_wait(bar, parity);
     parity ^= 1;
@@ -342,6 +346,9 @@ __global__ void __launch_bounds__(WARPS * 32) kvdp_hash_blocks_tma(const __grid_
       hash = avalanche(h);
     }
     __syncwarp();                     // every lane has read its row and has seen this phase complete
+    // this lane's generic-proxy reads (and, on the unaligned path, writes) of its row are ordered before the
+    // async-proxy bulk copy that overwrites the row next
+    fence_proxy_async_smem();
     if (t + 1 < t_end) issue(t + 1);  // the next tile's copies fly while this tile's results are stored
     if (valid) A.block_hash[gb] = hash;
   }
@@ -362,12 +369,12 @@ __global__ void __launch_bounds__(256) kvdp_hash_blocks_parts(const __grid_const
   constexpr int STEP = RPI * kPartsUnroll;
   const int lane = threadIdx.x & 31;
   const int sub = lane / P, part = lane % P;
-  const int64_t total = __ldg(A.block_offsets + A.n_req);
+  const int64_t b_begin = __ldg(A.block_offsets), total = __ldg(A.block_offsets + A.n_req);  // see kvdp_hash_blocks_tma
   const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
   const int64_t gw = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  int64_t per_warp = (total + warps_total - 1) / warps_total;
+  int64_t per_warp = (total - b_begin + warps_total - 1) / warps_total;
   per_warp = (per_warp + STEP - 1) / STEP * STEP;
-  const int64_t w_begin = min(total, gw * per_warp), w_end = min(total, w_begin + per_warp);
+  const int64_t w_begin = min(total, b_begin + gw * per_warp), w_end = min(total, w_begin + per_warp);
   if (w_begin >= w_end) return;
   // secret words of this lane's part (word index into S.w): first half of the block counts up, second half down
   const int sw = (part < (P + 1) / 2) ? 4 * part : 4 * (P - 1 - part) + 2;
@@ -432,10 +439,10 @@ __global__ void __launch_bounds__(256) kvdp_hash_blocks_parts(const __grid_const
 // ------------------------------------------------------------------------------------------------ generic block hash
 __global__ void __launch_bounds__(256) kvdp_hash_blocks_generic(const __grid_constant__ HashArgs A,
                                                                 const __grid_constant__ HashSecrets S) {
-  const int64_t total = __ldg(A.block_offsets + A.n_req);
+  const int64_t b_begin = __ldg(A.block_offsets), total = __ldg(A.block_offsets + A.n_req);  // see kvdp_hash_blocks_tma
   const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t gb = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gb < total; gb += nthreads) {
-    const int64_t r = find_request(A.block_offsets, A.n_req, gb & ~(int64_t)31, gb);
+  for (int64_t gb = b_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gb < total; gb += nthreads) {
+    const int64_t r = find_request(A.block_offsets, A.n_req, max(b_begin, gb & ~(int64_t)31), gb);
     WordReader in{A.tokens + __ldg(A.offsets + r) + (gb - __ldg(A.block_offsets + r)) * (int64_t)A.block_size};
     A.block_hash[gb] = xxh3_generic(in, (uint32_t)A.block_size * 4u, S);
   }
@@ -635,24 +642,120 @@ __global__ void kvdp_xxh3_batch_kernel(const uint8_t* __restrict__ data, int64_t
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-}  // namespace
-}  // namespace kvdp
-
-using namespace kvdp;
-
-extern "C" {
-
-size_t kvdp_hash_workspace_bytes(int64_t n_req) {
-  if (n_req < 0) n_req = 0;
+// ------------------------------------------------------------------------------------------------ host-side launches
+// Block-count scan over the whole batch (needs only the token offsets).
+int launch_scan(const int64_t* d_offsets, int64_t n_req, int32_t block_size, int64_t* d_block_offsets,
+                void* d_workspace, cudaStream_t stream) {
+  int64_t* partials = (int64_t*)d_workspace;
   const int64_t tiles = (n_req + 1 + kScanTile - 1) / kScanTile;
-  return align_up((size_t)(tiles + 1) * sizeof(int64_t), 256);
+  if (n_req + 1 <= kScanSmallMax) {
+    kvdp_block_count_scan_small<<<1, kScanSmallThreads, 0, stream>>>(d_offsets, n_req, block_size, d_block_offsets);
+  } else {
+    kvdp_block_count_scan_partials<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size,
+                                                                                 partials);
+    kvdp_block_count_scan_spine<<<1, kScanThreads, 0, stream>>>(partials, tiles);
+    kvdp_block_count_scan_apply<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size, partials,
+                                                                              d_block_offsets);
+  }
+  KVDP_CUDA(cudaGetLastError());
+  return 0;
 }
 
-int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, int64_t n_req, int64_t total_tokens,
+template <int NSTRIPES, int W>
+int launch_tma(const HashArgs& A, const HashSecrets& S, int64_t warp_tiles, const DevInfo& di, int dev,
+               cudaStream_t stream) {
+  const size_t smem = (size_t)W * 32 * (64 * NSTRIPES + 16) + 8 * W;
+  static std::mutex mu;
+  static bool attr_set[64] = {};  // the attribute is per device
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+      KVDP_CUDA(cudaFuncSetAttribute(kvdp_hash_blocks_tma<NSTRIPES, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+      if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+  }
+  const int64_t grid = std::min<int64_t>((warp_tiles + W - 1) / W, (int64_t)di.sm_count * 3);
+  kvdp_hash_blocks_tma<NSTRIPES, W><<<(unsigned)std::max<int64_t>(grid, 1), W * 32, smem, stream>>>(A, S);
+  return 0;
+}
+
+// Block hashes of the requests A describes (A may be a sub-range of the batch: shifted offset arrays, smaller n_req).
+// max_blocks = host-side upper bound of the number of blocks in that range; it only sizes the grid.
+int launch_block_hash(const HashArgs& A, const HashSecrets& S, int64_t max_blocks, const DevInfo& di, int dev,
+                      cudaStream_t stream) {
+  const int len = A.block_size * 4;
+  const int64_t warp_tiles = (max_blocks + 31) / 32;
+  if (len == 256) {
+    if (int rc = launch_tma<4, 8>(A, S, warp_tiles, di, dev, stream)) return rc;
+  } else if (len == 512) {
+    if (int rc = launch_tma<8, 4>(A, S, warp_tiles, di, dev, stream)) return rc;
+  } else if (len == 1024) {
+    if (int rc = launch_tma<16, 2>(A, S, warp_tiles, di, dev, stream)) return rc;
+  } else if (len == 16 || len == 32 || len == 64 || len == 128) {
+    const int64_t per_cta = 8 * (512 / len) * kPartsUnroll;  // blocks one CTA covers per loop trip
+    const int64_t grid =
+        std::max<int64_t>(1, std::min<int64_t>((max_blocks + per_cta - 1) / per_cta, (int64_t)di.sm_count * 8));
+    switch (len) {
+      case 16: kvdp_hash_blocks_parts<16><<<(unsigned)grid, 256, 0, stream>>>(A, S); break;
+      case 32: kvdp_hash_blocks_parts<32><<<(unsigned)grid, 256, 0, stream>>>(A, S); break;
+      case 64: kvdp_hash_blocks_parts<64><<<(unsigned)grid, 256, 0, stream>>>(A, S); break;
+      default: kvdp_hash_blocks_parts<128><<<(unsigned)grid, 256, 0, stream>>>(A, S); break;
+    }
+  } else {
+    const int64_t grid = std::min<int64_t>((max_blocks + 255) / 256, (int64_t)di.sm_count * 8);
+    kvdp_hash_blocks_generic<<<(unsigned)std::max<int64_t>(grid, 1), 256, 0, stream>>>(A, S);
+  }
+  KVDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_chain(const HashArgs& A, const HashSecrets& S, cudaStream_t stream) {
+  if (A.n_req <= 0) return 0;
+  kvdp_hash_chain<<<(unsigned)((A.n_req + kChainThreads - 1) / kChainThreads), kChainThreads, 0, stream>>>(A, S);
+  KVDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+HashArgs sub_range(const HashArgs& A, int64_t r0, int64_t r1) {
+  HashArgs B = A;
+  B.offsets = A.offsets + r0;
+  B.block_offsets = A.block_offsets + r0;
+  B.n_req = r1 - r0;
+  return B;
+}
+
+// Side streams for the staged form of a chained call: the chain kernel of one request range is latency-bound (one
+// thread per request, serial per request) and runs under the HBM-bound block-hash kernel of the next range.
+constexpr int kMaxHashStages = 16;
+struct HashFork {
+  std::mutex mu;
+  cudaStream_t side[2] = {nullptr, nullptr};
+  cudaEvent_t hashed[kMaxHashStages] = {};
+  cudaEvent_t chained[2] = {nullptr, nullptr};
+  bool ok = false;
+};
+HashFork g_fork[64];
+
+int fork_init(HashFork& f) {
+  if (f.ok) return 0;
+  int lo = 0, hi = 0;
+  KVDP_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));  // hi = numerically lowest = greatest priority
+  for (int i = 0; i < 2; ++i) {
+    KVDP_CUDA(cudaStreamCreateWithPriority(&f.side[i], cudaStreamNonBlocking, hi));
+    KVDP_CUDA(cudaEventCreateWithFlags(&f.chained[i], cudaEventDisableTiming));
+  }
+  for (int i = 0; i < kMaxHashStages; ++i) KVDP_CUDA(cudaEventCreateWithFlags(&f.hashed[i], cudaEventDisableTiming));
+  f.ok = true;
+  return 0;
+}
+
+// The body of kvdp_hash_token_blocks. `may_fork` = the call may use the library's side streams (created on the first
+// such call per device); the allocation-free entry point passes false and stays on the caller's stream alone.
+int hash_token_blocks_impl(const uint32_t* d_tokens, const int64_t* d_offsets, int64_t n_req, int64_t total_tokens,
                            int32_t block_size, uint64_t salt, int64_t* d_block_offsets, uint64_t* d_block_hash,
                            uint64_t* d_seq_hash, void* d_workspace, size_t workspace_bytes, uint32_t flags,
-                           kvdp_stream_t stream_) {
-  cudaStream_t stream = (cudaStream_t)stream_;
+                           cudaStream_t stream, bool may_fork) {
   if (n_req < 0 || total_tokens < 0) return fail(KVDP_EINVAL, "hash: negative n_req/total_tokens");
   if (block_size < 1) return fail(KVDP_EINVAL, "hash: block_size must be >= 1");
   if (!d_offsets || !d_block_offsets) return fail(KVDP_EINVAL, "hash: NULL offsets / block_offsets");
@@ -669,18 +772,7 @@ int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, i
   if (int rc = device_info(dev, &di)) return rc;
 
   // 1. block offsets
-  int64_t* partials = (int64_t*)d_workspace;
-  const int64_t tiles = (n_req + 1 + kScanTile - 1) / kScanTile;
-  if (n_req + 1 <= kScanSmallMax) {
-    kvdp_block_count_scan_small<<<1, kScanSmallThreads, 0, stream>>>(d_offsets, n_req, block_size, d_block_offsets);
-  } else {
-    kvdp_block_count_scan_partials<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size,
-                                                                                 partials);
-    kvdp_block_count_scan_spine<<<1, kScanThreads, 0, stream>>>(partials, tiles);
-    kvdp_block_count_scan_apply<<<(unsigned)tiles, kScanThreads, 0, stream>>>(d_offsets, n_req, block_size, partials,
-                                                                              d_block_offsets);
-  }
-  KVDP_CUDA(cudaGetLastError());
+  if (int rc = launch_scan(d_offsets, n_req, block_size, d_block_offsets, d_workspace, stream)) return rc;
 
   const int64_t max_blocks = total_tokens / block_size;
   if (max_blocks == 0 || n_req == 0) return 0;
@@ -697,63 +789,71 @@ int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, i
   A.flags = flags;
   const HashSecrets S = make_secrets(salt);
 
-  // 2. block hashes
-  const int len = block_size * 4;
-  const int64_t warp_tiles = (max_blocks + 31) / 32;
-  if (len == 256) {
-    constexpr int W = 8;
-    const size_t smem = (size_t)W * 32 * (256 + 16) + 8 * W;
-    static bool attr_set[64] = {};  // the attribute is per device
-    if (dev >= 64 || !attr_set[dev]) {
-      KVDP_CUDA(cudaFuncSetAttribute(kvdp_hash_blocks_tma<4, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)smem));
-      if (dev < 64) attr_set[dev] = true;
-    }
-    const int64_t grid = std::min<int64_t>((warp_tiles + W - 1) / W, (int64_t)di.sm_count * 3);
-    kvdp_hash_blocks_tma<4, W><<<(unsigned)std::max<int64_t>(grid, 1), W * 32, smem, stream>>>(A, S);
-  } else if (len == 512) {
-    constexpr int W = 4;
-    const size_t smem = (size_t)W * 32 * (512 + 16) + 8 * W;
-    static bool attr_set[64] = {};  // the attribute is per device
-    if (dev >= 64 || !attr_set[dev]) {
-      KVDP_CUDA(cudaFuncSetAttribute(kvdp_hash_blocks_tma<8, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)smem));
-      if (dev < 64) attr_set[dev] = true;
-    }
-    const int64_t grid = std::min<int64_t>((warp_tiles + W - 1) / W, (int64_t)di.sm_count * 3);
-    kvdp_hash_blocks_tma<8, W><<<(unsigned)std::max<int64_t>(grid, 1), W * 32, smem, stream>>>(A, S);
-  } else if (len == 1024) {
-    constexpr int W = 2;
-    const size_t smem = (size_t)W * 32 * (1024 + 16) + 8 * W;
-    static bool attr_set[64] = {};  // the attribute is per device
-    if (dev >= 64 || !attr_set[dev]) {
-      KVDP_CUDA(cudaFuncSetAttribute(kvdp_hash_blocks_tma<16, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)smem));
-      if (dev < 64) attr_set[dev] = true;
-    }
-    const int64_t grid = std::min<int64_t>((warp_tiles + W - 1) / W, (int64_t)di.sm_count * 3);
-    kvdp_hash_blocks_tma<16, W><<<(unsigned)std::max<int64_t>(grid, 1), W * 32, smem, stream>>>(A, S);
-  } else if (len == 16 || len == 32 || len == 64 || len == 128) {
-    const int64_t per_cta = 8 * (512 / len) * kPartsUnroll;  // blocks one CTA covers per loop trip
-    const int64_t grid = std::max<int64_t>(1, std::min<int64_t>((max_blocks + per_cta - 1) / per_cta, (int64_t)di.sm_count * 8));
-    switch (len) {
-      case 16: kvdp_hash_blocks_parts<16><<<(unsigned)grid, 256, 0, stream>>>(A, S); break;
-      case 32: kvdp_hash_blocks_parts<32><<<(unsigned)grid, 256, 0, stream>>>(A, S); break;
-      case 64: kvdp_hash_blocks_parts<64><<<(unsigned)grid, 256, 0, stream>>>(A, S); break;
-      default: kvdp_hash_blocks_parts<128><<<(unsigned)grid, 256, 0, stream>>>(A, S); break;
-    }
-  } else {
-    const int64_t grid = std::min<int64_t>((max_blocks + 255) / 256, (int64_t)di.sm_count * 8);
-    kvdp_hash_blocks_generic<<<(unsigned)std::max<int64_t>(grid, 1), 256, 0, stream>>>(A, S);
+  // 2 + 3. block hashes, then the chain. A big chained batch is cut into request ranges: the chain of range k runs
+  // on a side stream under the block hashing of range k+1 and is joined back onto the caller's stream at the end, so
+  // the caller sees one ordered call. Only the last range's chain is not hidden.
+  int stages = (int)options().hash_stages;
+  if (stages <= 0) stages = 4;
+  stages = std::min(stages, kMaxHashStages);
+  const bool staged = may_fork && d_seq_hash && stages > 1 && dev >= 0 && dev < 64 && n_req >= 4096 &&
+                      (int64_t)max_blocks * block_size * 4 >= ((int64_t)64 << 20);
+  if (!staged) {
+    if (int rc = launch_block_hash(A, S, max_blocks, di, dev, stream)) return rc;
+    if (d_seq_hash)
+      if (int rc = launch_chain(A, S, stream)) return rc;
+    return 0;
   }
-  KVDP_CUDA(cudaGetLastError());
-
-  // 3. chain
-  if (d_seq_hash) {
-    kvdp_hash_chain<<<(unsigned)((n_req + kChainThreads - 1) / kChainThreads), kChainThreads, 0, stream>>>(A, S);
-    KVDP_CUDA(cudaGetLastError());
+  HashFork& f = g_fork[dev];
+  std::lock_guard<std::mutex> lk(f.mu);  // a fork/join sequence is enqueued as a whole
+  if (int rc = fork_init(f)) return rc;
+  for (int k = 0; k < stages; ++k) {
+    const int64_t r0 = n_req * k / stages, r1 = n_req * (k + 1) / stages;
+    if (r1 <= r0) continue;
+    const HashArgs B = sub_range(A, r0, r1);
+    // the host does not see the offsets: size each range's grid for its share of the batch, with headroom
+    const int64_t range_blocks = std::min<int64_t>(max_blocks, max_blocks / stages * 2 + 1024);
+    if (int rc = launch_block_hash(B, S, range_blocks, di, dev, stream)) return rc;
+    KVDP_CUDA(cudaEventRecord(f.hashed[k], stream));
+    cudaStream_t side = f.side[k & 1];
+    KVDP_CUDA(cudaStreamWaitEvent(side, f.hashed[k], 0));
+    if (int rc = launch_chain(B, S, side)) return rc;
+  }
+  for (int i = 0; i < 2; ++i) {
+    KVDP_CUDA(cudaEventRecord(f.chained[i], f.side[i]));
+    KVDP_CUDA(cudaStreamWaitEvent(stream, f.chained[i], 0));
   }
   return 0;
+}
+
+}  // namespace
+
+// used by hash_static.cu: the same kernels on the caller's stream only (no side streams, nothing created)
+int hash_token_blocks_single_stream(const uint32_t* d_tokens, const int64_t* d_offsets, int64_t n_req,
+                                    int64_t total_tokens, int32_t block_size, uint64_t salt, int64_t* d_block_offsets,
+                                    uint64_t* d_block_hash, uint64_t* d_seq_hash, void* d_workspace,
+                                    size_t workspace_bytes, uint32_t flags, cudaStream_t stream) {
+  return hash_token_blocks_impl(d_tokens, d_offsets, n_req, total_tokens, block_size, salt, d_block_offsets,
+                                d_block_hash, d_seq_hash, d_workspace, workspace_bytes, flags, stream, false);
+}
+}  // namespace kvdp
+
+using namespace kvdp;
+
+extern "C" {
+
+size_t kvdp_hash_workspace_bytes(int64_t n_req) {
+  if (n_req < 0) n_req = 0;
+  const int64_t tiles = (n_req + 1 + kScanTile - 1) / kScanTile;
+  return align_up((size_t)(tiles + 1) * sizeof(int64_t), 256);
+}
+
+int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, int64_t n_req, int64_t total_tokens,
+                           int32_t block_size, uint64_t salt, int64_t* d_block_offsets, uint64_t* d_block_hash,
+                           uint64_t* d_seq_hash, void* d_workspace, size_t workspace_bytes, uint32_t flags,
+                           kvdp_stream_t stream_) {
+  return hash_token_blocks_impl(d_tokens, d_offsets, n_req, total_tokens, block_size, salt, d_block_offsets,
+                                d_block_hash, d_seq_hash, d_workspace, workspace_bytes, flags, (cudaStream_t)stream_,
+                                true);
 }
 
 int kvdp_xxh3_64_batch(const uint8_t* d_data, int64_t n, int64_t len, uint64_t seed, uint64_t* d_out,
@@ -771,7 +871,8 @@ int kvdp_xxh3_64_batch(const uint8_t* d_data, int64_t n, int64_t len, uint64_t s
 namespace {
 struct HostHashCtx {
   std::mutex mu;
-  cudaStream_t stream = nullptr;
+  cudaStream_t up = nullptr, compute = nullptr, down = nullptr;
+  cudaEvent_t uploaded = nullptr, hashed = nullptr, scanned = nullptr;
   void* d_tokens = nullptr;
   size_t tok_cap = 0;
   void* d_req = nullptr;  // offsets + block_offsets
@@ -793,20 +894,37 @@ int ensure(void** p, size_t* cap, size_t need) {
   *cap = sz;
   return 0;
 }
+
+constexpr int64_t kHostChunkTokens = (int64_t)1 << 20;  // 4 MiB of tokens per pipeline step
 }  // namespace
 
+// Upload, hashing and download overlap: the batch is cut at request boundaries into pieces of about 4 MiB of tokens;
+// piece k is hashed (and chained) on the compute stream while piece k+1 is still on its way up and the results of piece
+// k-1 are on their way down, each on a stream of its own. With pinned host buffers the call runs at the speed of the
+// host->device link; pageable buffers work too (the driver stages them).
 int kvdp_hash_token_blocks_host(const uint32_t* h_tokens, const int64_t* h_offsets, int64_t n_req, int32_t block_size,
                                 uint64_t salt, int64_t* h_block_offsets, uint64_t* h_block_hash, uint64_t* h_seq_hash,
                                 uint32_t flags, int32_t device) {
   if (n_req < 0 || !h_offsets || !h_block_offsets) return fail(KVDP_EINVAL, "hash(host): bad arguments");
   if (block_size < 1) return fail(KVDP_EINVAL, "hash(host): block_size must be >= 1");
+  if ((uint64_t)block_size * 4 >= ((uint64_t)1 << 31)) return fail(KVDP_ERANGE, "hash: block_size too large");
+  if (flags & ~KVDP_HASH_TWIN_FIRST) return fail(KVDP_EINVAL, "hash: unknown flags 0x%x", flags);
   if (device < 0) KVDP_CUDA(cudaGetDevice(&device));
   if (device >= 64) return fail(KVDP_EINVAL, "device ordinal %d not supported", device);
-  // validate offsets on the host (the device path trusts them)
-  int64_t total_blocks = 0;
+  // validate offsets on the host (the device path trusts them) and cut the batch into pieces
+  struct Piece {
+    int64_t r0, r1, b0, b1;
+  };
+  std::vector<Piece> pieces;
+  int64_t total_blocks = 0, piece_r0 = 0, piece_b0 = 0;
   for (int64_t r = 0; r < n_req; ++r) {
     if (h_offsets[r + 1] < h_offsets[r]) return fail(KVDP_EINVAL, "hash(host): offsets must be non-decreasing");
     total_blocks += (h_offsets[r + 1] - h_offsets[r]) / block_size;
+    if (h_offsets[r + 1] - h_offsets[piece_r0] >= kHostChunkTokens || r + 1 == n_req) {
+      pieces.push_back({piece_r0, r + 1, piece_b0, total_blocks});
+      piece_r0 = r + 1;
+      piece_b0 = total_blocks;
+    }
   }
   const int64_t tok_begin = h_offsets[0], tok_end = h_offsets[n_req];
   const int64_t total_tokens = tok_end;  // offsets index into h_tokens from 0
@@ -815,9 +933,18 @@ int kvdp_hash_token_blocks_host(const uint32_t* h_tokens, const int64_t* h_offse
   if (total_blocks > 0 && !h_block_hash) return fail(KVDP_EINVAL, "hash(host): NULL block_hash");
 
   DeviceGuard g(device);
+  DevInfo di;
+  if (int rc = device_info(device, &di)) return rc;
   HostHashCtx& c = g_host_ctx[device];
   std::lock_guard<std::mutex> lk(c.mu);
-  if (!c.stream) KVDP_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+  if (!c.up) {
+    KVDP_CUDA(cudaStreamCreateWithFlags(&c.up, cudaStreamNonBlocking));
+    KVDP_CUDA(cudaStreamCreateWithFlags(&c.compute, cudaStreamNonBlocking));
+    KVDP_CUDA(cudaStreamCreateWithFlags(&c.down, cudaStreamNonBlocking));
+    KVDP_CUDA(cudaEventCreateWithFlags(&c.uploaded, cudaEventDisableTiming));
+    KVDP_CUDA(cudaEventCreateWithFlags(&c.hashed, cudaEventDisableTiming));
+    KVDP_CUDA(cudaEventCreateWithFlags(&c.scanned, cudaEventDisableTiming));
+  }
   if (int rc = ensure(&c.d_tokens, &c.tok_cap, (size_t)total_tokens * 4 + 16)) return rc;
   if (int rc = ensure(&c.d_req, &c.req_cap, (size_t)(n_req + 1) * 16)) return rc;
   if (int rc = ensure(&c.d_out, &c.out_cap, (size_t)total_blocks * 16 + 16)) return rc;
@@ -827,19 +954,47 @@ int kvdp_hash_token_blocks_host(const uint32_t* h_tokens, const int64_t* h_offse
   int64_t* d_boff = d_off + (n_req + 1);
   uint64_t* d_bh = (uint64_t*)c.d_out;
   uint64_t* d_sh = d_bh + total_blocks;
-  if (total_tokens > 0)
-    KVDP_CUDA(cudaMemcpyAsync(c.d_tokens, h_tokens, (size_t)total_tokens * 4, cudaMemcpyHostToDevice, c.stream));
-  KVDP_CUDA(cudaMemcpyAsync(d_off, h_offsets, (size_t)(n_req + 1) * 8, cudaMemcpyHostToDevice, c.stream));
-  if (int rc = kvdp_hash_token_blocks((const uint32_t*)c.d_tokens, d_off, n_req, total_tokens, block_size, salt, d_boff,
-                                      d_bh, h_seq_hash ? d_sh : nullptr, c.d_ws, c.ws_cap, flags, c.stream))
-    return rc;
-  KVDP_CUDA(cudaMemcpyAsync(h_block_offsets, d_boff, (size_t)(n_req + 1) * 8, cudaMemcpyDeviceToHost, c.stream));
-  if (total_blocks > 0) {
-    KVDP_CUDA(cudaMemcpyAsync(h_block_hash, d_bh, (size_t)total_blocks * 8, cudaMemcpyDeviceToHost, c.stream));
+  const uint32_t* d_tok = (const uint32_t*)c.d_tokens;
+
+  // offsets first (small), then the block-count scan; its result goes down while the token pieces go up
+  KVDP_CUDA(cudaMemcpyAsync(d_off, h_offsets, (size_t)(n_req + 1) * 8, cudaMemcpyHostToDevice, c.compute));
+  if (int rc = launch_scan(d_off, n_req, block_size, d_boff, c.d_ws, c.compute)) return rc;
+  KVDP_CUDA(cudaEventRecord(c.scanned, c.compute));
+  KVDP_CUDA(cudaStreamWaitEvent(c.down, c.scanned, 0));
+  KVDP_CUDA(cudaMemcpyAsync(h_block_offsets, d_boff, (size_t)(n_req + 1) * 8, cudaMemcpyDeviceToHost, c.down));
+
+  HashArgs A;
+  A.tokens = d_tok;
+  A.offsets = d_off;
+  A.block_offsets = d_boff;
+  A.block_hash = d_bh;
+  A.seq_hash = h_seq_hash ? d_sh : nullptr;
+  A.n_req = n_req;
+  A.block_size = block_size;
+  A.flags = flags;
+  const HashSecrets S = make_secrets(salt);
+  for (const Piece& p : pieces) {
+    const int64_t t0 = h_offsets[p.r0], t1 = h_offsets[p.r1];
+    if (t1 > t0)
+      KVDP_CUDA(cudaMemcpyAsync((void*)(d_tok + t0), h_tokens + t0, (size_t)(t1 - t0) * 4, cudaMemcpyHostToDevice, c.up));
+    if (p.b1 == p.b0) continue;
+    KVDP_CUDA(cudaEventRecord(c.uploaded, c.up));
+    KVDP_CUDA(cudaStreamWaitEvent(c.compute, c.uploaded, 0));
+    const HashArgs B = sub_range(A, p.r0, p.r1);
+    if (int rc = launch_block_hash(B, S, p.b1 - p.b0, di, device, c.compute)) return rc;
     if (h_seq_hash)
-      KVDP_CUDA(cudaMemcpyAsync(h_seq_hash, d_sh, (size_t)total_blocks * 8, cudaMemcpyDeviceToHost, c.stream));
+      if (int rc = launch_chain(B, S, c.compute)) return rc;
+    KVDP_CUDA(cudaEventRecord(c.hashed, c.compute));
+    KVDP_CUDA(cudaStreamWaitEvent(c.down, c.hashed, 0));
+    KVDP_CUDA(cudaMemcpyAsync(h_block_hash + p.b0, d_bh + p.b0, (size_t)(p.b1 - p.b0) * 8, cudaMemcpyDeviceToHost,
+                              c.down));
+    if (h_seq_hash)
+      KVDP_CUDA(cudaMemcpyAsync(h_seq_hash + p.b0, d_sh + p.b0, (size_t)(p.b1 - p.b0) * 8, cudaMemcpyDeviceToHost,
+                                c.down));
   }
-  KVDP_CUDA(cudaStreamSynchronize(c.stream));
+  KVDP_CUDA(cudaStreamSynchronize(c.up));
+  KVDP_CUDA(cudaStreamSynchronize(c.compute));
+  KVDP_CUDA(cudaStreamSynchronize(c.down));
   return 0;
 }
 

@@ -45,7 +45,9 @@ int kvdp_version(void);
  * vectors for chunks <= 4 KiB),
  * "tile_bytes", "stages", "ctas_per_sm", "host_path" (pinned memory: 0 vector kernel, 1 DMA loop, 2 TMA kernel), "host_ctas", "l2_hint",
  * "vec32" (copy path 1: 256-bit loads/stores when every pointer and stride is 32-byte aligned; +5 % on that path in HBM,
- * no change over NVLink). Returns KVDP_EINVAL for
+ * no change over NVLink), "hash_stages" (chained hashing of a big batch: number of request ranges whose chain kernels
+ * run under the next range's block hashing; 0 = default 4, 1 = one range, nothing leaves the caller's stream).
+ * Returns KVDP_EINVAL for
  * unknown names. Intended for benchmarking; defaults are what the tests run. */
 int kvdp_set_option(const char* name, int64_t value);
 int64_t kvdp_get_option(const char* name);
@@ -241,7 +243,11 @@ int kvdp_host_tier_sync(kvdp_host_tier* t);
 #define KVDP_HASH_TWIN_FIRST 1u
 size_t kvdp_hash_workspace_bytes(int64_t n_req);
 /* all pointers are device pointers; seq_hash may be NULL (un-chained only). total_tokens = offsets[n_req] as known to
- * the host (sizes the grid). */
+ * the host (sizes the grid). Asynchronous and ordered on `stream` like one kernel. Internally a big chained batch
+ * (>= 4096 requests, >= 64 MiB of tokens) is cut into request ranges: the serial, latency-bound chain kernel of one
+ * range runs on a library-owned side stream under the HBM-bound block hashing of the next range and is joined back
+ * onto `stream` before the call's work counts as complete (streams and events are created on the first such call per
+ * device). The result is the same bits either way. */
 int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, int64_t n_req, int64_t total_tokens,
                            int32_t block_size, uint64_t salt, int64_t* d_block_offsets, uint64_t* d_block_hash,
                            uint64_t* d_seq_hash, void* d_workspace, size_t workspace_bytes, uint32_t flags,

@@ -214,3 +214,57 @@ def test_random_batches_block_sizes_and_salts_vs_oracle(gpu, oracle, seed):
     boff, bh, sh = hash_token_blocks(toks, offs, bs, salt)
     w_off, w_bh, w_sh = oracle.hash_batch(toks, offs, bs, salt, threads=4)
     assert np.array_equal(boff, w_off) and np.array_equal(bh, w_bh) and np.array_equal(sh, w_sh), (bs, n_req, salt)
+
+
+@pytest.mark.parametrize("bs,twin", [(64, False), (16, False), (24, True), (128, False)])
+def test_staged_chained_call_and_pipelined_host_form_vs_oracle(gpu, oracle, bs, twin):
+    """A batch big enough (6 000 requests, ~19 M tokens) that (a) the device-pointer call cuts it into request ranges and
+    runs their chain kernels on side streams under the next range's block hashing, for every `hash_stages` setting, and
+    (b) the host-buffer call moves it in ~18 pieces with upload, hashing and download overlapped. Ragged lengths with
+    empty requests and starts off the 16-byte grid; every output word against the oracle."""
+    rng = np.random.Generator(np.random.PCG64(bs))
+    lens = rng.integers(0, 6400, size=6000).astype(np.int64)
+    lens[rng.integers(0, lens.size, size=200)] = 0
+    lens[::5] = (lens[::5] // 64) * 64
+    offs = np.zeros(lens.size + 1, dtype=np.int64)
+    offs[1:] = np.cumsum(lens)
+    toks = tokens_for(11, int(offs[-1]))
+    want = oracle.hash_batch(toks, offs, bs, 1337, oracle.hw_threads())
+    if twin:          # the oracle's batch form has no twin flag: apply the quirk per request (first block onto parent 0)
+        want = None
+    L = gpu.lib()
+    n_req, total = lens.size, int(offs[-1])
+    nblk = int((lens // bs).sum())
+    d_tok, d_off = DevBuf(gpu, toks.nbytes), DevBuf(gpu, offs.nbytes)
+    d_boff, d_bh, d_sh = DevBuf(gpu, (n_req + 1) * 8), DevBuf(gpu, nblk * 8), DevBuf(gpu, nblk * 8)
+    ws_bytes = L.kvdp_hash_workspace_bytes(n_req)
+    d_ws = DevBuf(gpu, ws_bytes)
+    d_tok.upload(toks)
+    d_off.upload(offs)
+    flags = gpu.HASH_TWIN_FIRST if twin else 0
+    results = []
+    try:
+        for stages in (1, 0, 2, 7, 16):
+            gpu.set_option("hash_stages", stages)
+            gpu.check(L.kvdp_memset(d_bh.ptr, 0, nblk * 8))
+            gpu.check(L.kvdp_memset(d_sh.ptr, 0, nblk * 8))
+            gpu.check(L.kvdp_hash_token_blocks(d_tok.ptr, d_off.ptr, n_req, total, bs, 1337, d_boff.ptr, d_bh.ptr,
+                                               d_sh.ptr, d_ws.ptr, ws_bytes, flags, None))
+            gpu.check(L.kvdp_stream_synchronize(None))
+            results.append((d_boff.download(np.int64), d_bh.download(np.uint64), d_sh.download(np.uint64)))
+    finally:
+        gpu.set_option("hash_stages", 0)
+    for got in results[1:]:
+        assert all(np.array_equal(a, b) for a, b in zip(got, results[0]))      # staged == single stream, bit for bit
+    host = hash_token_blocks(toks, offs, bs, 1337, twin_first_block=twin)       # pipelined host-buffer form
+    assert all(np.array_equal(a, b) for a, b in zip(host, results[0]))
+    if want is not None:
+        assert all(np.array_equal(a, b) for a, b in zip(results[0], want))
+    else:
+        ref_off, ref_bh, ref_sh = oracle.hash_batch(toks, offs, bs, 1337, oracle.hw_threads())
+        assert np.array_equal(results[0][0], ref_off) and np.array_equal(results[0][1], ref_bh)
+        r = int(np.argmax(lens // bs >= 3))                                      # one request spelled out with the quirk
+        b0 = int(ref_off[r])
+        _, _, one = hash_token_blocks(toks[offs[r]:offs[r + 1]], np.array([0, lens[r]]), bs, 1337, twin_first_block=True)
+        assert np.array_equal(results[0][2][b0:b0 + one.size], one)
+        assert one[0] != ref_sh[b0]
