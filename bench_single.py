@@ -140,18 +140,21 @@ def e2e_legacy(torch, lib, args, steps, warmup):
     ONBOARDS one batch of blocks (pinned host layer-separate cache -> HBM cache) and OFFLOADS another batch of the same
     size (HBM cache -> pinned host cache), each through its own CopyStream, as the reference's pool of CopyStreams
     allows; the two directions share the PCIe link in opposite directions. value = payload of both batches / wall time.
-    Each direction is also timed alone against its own link ceiling."""
+    Each direction is also timed alone against its own link ceiling. Block ids: the host caches hold twice the batch;
+    every request's 64 blocks sit next to each other on the host side at a random request slot (how a host tier stores
+    an offloaded request), the device-side ids are a random permutation. A second, fully scattered id set (random host
+    blocks, no runs) is timed beside it."""
     L = lib.lib()
     pairs = BLOCKS_PER_REQ * args.requests
-    nh = nd = pairs
-    layer_bytes = 2 * nh * CHUNK
+    nd, nh = pairs, 2 * pairs
+    layer_bytes, host_layer_bytes = 2 * nd * CHUNK, 2 * nh * CHUNK
 
     def pinned_layers(fill):
         arrs, ptrs = [], []
         for l in range(L8B):
             p = C.c_void_p()
-            lib.check(L.cuda_malloc_host(C.byref(p), layer_bytes))
-            a = np.frombuffer((C.c_uint8 * layer_bytes).from_address(p.value), dtype=np.uint8)
+            lib.check(L.cuda_malloc_host(C.byref(p), host_layer_bytes))
+            a = np.frombuffer((C.c_uint8 * host_layer_bytes).from_address(p.value), dtype=np.uint8)
             if fill:
                 w = a.view(np.uint64)
                 w[:] = np.arange(w.size, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15) + np.uint64(l)
@@ -173,8 +176,16 @@ def e2e_legacy(torch, lib, args, steps, warmup):
     rng = np.random.Generator(np.random.PCG64(77))
     suffix = BS * H8B * D8B
 
-    def one_step(onboard=True, offload=True):
-        ids = [rng.permutation(nh).astype(np.int32) for _ in range(4)]
+    def host_ids(scattered):
+        if scattered:
+            return rng.permutation(nh)[:pairs].astype(np.int32)
+        slots = rng.permutation(nh // BLOCKS_PER_REQ)[:args.requests]
+        return np.concatenate([np.arange(s * BLOCKS_PER_REQ, (s + 1) * BLOCKS_PER_REQ) for s in slots]).astype(np.int32)
+
+    def one_step(onboard=True, offload=True, scattered=False):
+        # (onboard src = host, dst = device; offload src = device, dst = host)
+        ids = [host_ids(scattered), rng.permutation(nd).astype(np.int32), rng.permutation(nd).astype(np.int32),
+               host_ids(scattered)]
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         if onboard:
@@ -210,15 +221,19 @@ def e2e_legacy(torch, lib, args, steps, warmup):
     t_on = min(one_step(True, False)[0] for _ in range(3))
     one_step(False, True)
     t_off = min(one_step(False, True)[0] for _ in range(3))
+    one_step(scattered=True)
+    t_sc = min(one_step(scattered=True)[0] for _ in range(2))
+    t_sc_on = min(one_step(True, False, True)[0] for _ in range(2))
+    t_sc_off = min(one_step(False, True, True)[0] for _ in range(2))
     # comparator: the same call sequence with the reference's data movement behind it, one cudaMemcpyAsync per
     # (K|V, pair) chunk (block_copy.cu:246-305), which libkvdp keeps as host_path = 1
     dma_loop = None
     if lib.get_option("host_path") == 0:
         lib.set_option("host_path", 1)
-        dma_loop = pairs * BLOCK_BYTES / min(one_step(True, False)[0] for _ in range(2)) / GB
+        dma_loop = pairs * BLOCK_BYTES / min(one_step(True, False, True)[0] for _ in range(2)) / GB
         lib.set_option("host_path", 0)
     # practical ceilings of the host link on this box: contiguous 1 GiB pinned DMAs, each way alone and both at once
-    n_c = min(1 << 30, layer_bytes * 4)
+    n_c = 1 << 30
     big_h = C.c_void_p()
     lib.check(L.cuda_malloc_host(C.byref(big_h), 2 * n_c))
     big_d = torch.empty(2 * n_c, dtype=torch.uint8, device="cuda")
@@ -254,8 +269,15 @@ def e2e_legacy(torch, lib, args, steps, warmup):
             "offload": {"GBps": payload / t_off / GB, "d2h_link_ceiling_GBps": ceil_d2h,
                         "frac_of_link_ceiling": payload / t_off / GB / ceil_d2h},
             "h2d_link_ceiling_GBps": ceil_h2d, "frac_of_link_ceiling": payload / t_on / GB / ceil_h2d,
-            "host_path": "kernel zero-copy (SMs read / write pinned memory)" if lib.get_option("host_path") == 0
-            else "per-chunk cudaMemcpyAsync loop",
+            "host_path": {0: "auto: one DMA per run of consecutive host blocks through HBM staging + one kernel per layer "
+                             "when the host-side runs average >= 1 MiB, else SMs read / write pinned memory",
+                          1: "per-chunk cudaMemcpyAsync loop", 2: "TMA kernel on pinned memory",
+                          3: "SMs read / write pinned memory"}[lib.get_option("host_path")],
+            "scattered_host_ids": {"both_GBps": 2 * payload / t_sc / GB, "onboard_GBps": payload / t_sc_on / GB,
+                                   "offload_GBps": payload / t_sc_off / GB,
+                                   "note": "512 random host blocks out of 1024 (no runs): zero-copy kernels; SM accesses "
+                                           "to host memory are 128-byte PCIe requests (0.92 of the link, "
+                                           "profiles/sweep_r02_host_paths.txt)"},
             "verification": "all bytes of the last step, both directions",
             "per_chunk_dma_loop_GBps": dma_loop,
             "per_chunk_dma_loop_note": "onboard alone with the reference's data movement behind the same ABI calls (one "

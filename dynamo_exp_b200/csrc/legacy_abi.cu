@@ -7,12 +7,36 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 #include <vector>
 
 #include "plan_xfer.cuh"
 
 using namespace kvdp;
+
+// Pinned-host endpoints whose block ids form long consecutive runs on the host side (a host tier stores the blocks of a
+// request next to each other) are moved by the copy engines: one cudaMemcpyAsync per run between host memory and a
+// two-slot HBM staging buffer on a side stream, and one kernel launch between staging and the scattered device blocks.
+// SM loads / stores on host memory top out at 0.92 of the link (128-byte PCIe requests; every grid / tile / TMA setting
+// measured the same, profiles/sweep_r02_host_paths.txt) and their reads collapse when the other direction is busy
+// (profiles/duplex_r02.txt); the DMA path reaches the link's own rate in both directions at once.
+struct HostDma {
+  cudaStream_t dma = nullptr;
+  cudaEvent_t filled[2] = {}, drained[2] = {};  // staging slot: producer done / consumer done
+  bool drained_valid[2] = {false, false};
+  cudaEvent_t tail = nullptr;                     // last DMA enqueued (offload: the data is on the host after it)
+  bool tail_valid = false;
+  void* staging[2] = {nullptr, nullptr};
+  size_t cap = 0;
+  int next = 0;
+  IdStage ids;              // identity positions + the device-side ids in host-sorted order
+  bool ids_ok = false;
+  bool ids_current = false;  // the device copy of the sorted ids matches the current id set
+  int sorted_for = 0;       // 0 = not computed for the current id set, 1 = sorted by src ids, 2 = by dst ids
+  std::vector<int> order;   // pair indices sorted by the host-side id
+  std::vector<int> run_pos, run_len;  // maximal runs of consecutive host ids, as positions in `order`
+};
 
 struct CopyStream {
   IdStage ids;
@@ -22,6 +46,7 @@ struct CopyStream {
   int num_layers = 0;
   int device = -1;
   bool ok = false;
+  HostDma hd;
 };
 
 namespace {
@@ -114,6 +139,141 @@ int dma_loop_3d(const void* src, void* dst, const int* h_sids, const int* h_dids
   return 0;
 }
 
+// ---- coalesced-DMA host path of a CopyStream ------------------------------------------------------------------
+void host_dma_destroy(HostDma& h) {
+  if (h.dma) cudaStreamSynchronize(h.dma);
+  for (int i = 0; i < 2; ++i) {
+    if (h.staging[i]) cudaFree(h.staging[i]);
+    if (h.filled[i]) cudaEventDestroy(h.filled[i]);
+    if (h.drained[i]) cudaEventDestroy(h.drained[i]);
+    h.staging[i] = nullptr;
+  }
+  if (h.tail) cudaEventDestroy(h.tail);
+  if (h.ids_ok) h.ids.destroy();
+  if (h.dma) cudaStreamDestroy(h.dma);
+  h = HostDma();
+}
+
+// Sort the pairs by their host-side id and find the runs; decide whether the DMA path pays (average run >= 1 MiB).
+bool host_dma_plan(CopyStream* cs, bool host_is_src, size_t chunk_bytes) {
+  HostDma& h = cs->hd;
+  const int want = host_is_src ? 1 : 2;
+  const int n = cs->num_blocks;
+  if (h.sorted_for != want) {
+    const std::vector<int>& key = host_is_src ? cs->h_src : cs->h_dst;
+    h.order.resize(n);
+    for (int i = 0; i < n; ++i) h.order[i] = i;
+    std::stable_sort(h.order.begin(), h.order.end(), [&key](int a, int b) { return key[a] < key[b]; });
+    h.run_pos.clear();
+    h.run_len.clear();
+    for (int k = 0; k < n; ++k) {
+      if (k > 0 && key[h.order[k]] == key[h.order[k - 1]] + 1)
+        ++h.run_len.back();
+      else {
+        h.run_pos.push_back(k);
+        h.run_len.push_back(1);
+      }
+    }
+    h.sorted_for = want;
+    h.ids_current = false;
+  }
+  return !h.run_pos.empty() && (double)n * (double)chunk_bytes / (double)h.run_pos.size() >= (double)(1 << 20);
+}
+
+int host_dma_prepare(CopyStream* cs, bool host_is_src, size_t need_bytes) {
+  HostDma& h = cs->hd;
+  if (!h.dma) {
+    KVDP_CUDA(cudaStreamCreateWithFlags(&h.dma, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      KVDP_CUDA(cudaEventCreateWithFlags(&h.filled[i], cudaEventDisableTiming));
+      KVDP_CUDA(cudaEventCreateWithFlags(&h.drained[i], cudaEventDisableTiming));
+    }
+    KVDP_CUDA(cudaEventCreateWithFlags(&h.tail, cudaEventDisableTiming));
+  }
+  if (!h.ids_ok) {
+    if (int rc = h.ids.init(std::max(cs->num_blocks, 1), cs->device)) return rc;
+    h.ids_ok = true;
+  }
+  if (h.cap < need_bytes) {
+    KVDP_CUDA(cudaStreamSynchronize(h.dma));
+    KVDP_CUDA(cudaStreamSynchronize(cs->stream));
+    for (int i = 0; i < 2; ++i) {
+      if (h.staging[i]) KVDP_CUDA(cudaFree(h.staging[i]));
+      h.staging[i] = nullptr;
+      h.drained_valid[i] = false;
+    }
+    h.cap = 0;
+    for (int i = 0; i < 2; ++i) KVDP_CUDA(cudaMalloc(&h.staging[i], need_bytes));
+    h.cap = need_bytes;
+  }
+  if (!h.ids_current) {  // device copy of (position, device-side id in host-sorted order), once per id set
+    const int n = cs->num_blocks;
+    std::vector<int32_t> pos(n), other(n);
+    const std::vector<int>& dev_ids = host_is_src ? cs->h_dst : cs->h_src;
+    for (int k = 0; k < n; ++k) {
+      pos[k] = k;
+      other[k] = dev_ids[h.order[k]];
+    }
+    // as (src, dst) of the staging<->device kernel: onboard reads staging positions, offload writes them
+    if (int rc = host_is_src ? h.ids.upload(pos.data(), other.data(), n, cs->stream)
+                             : h.ids.upload(other.data(), pos.data(), n, cs->stream))
+      return rc;
+    h.ids_current = true;
+  }
+  return 0;
+}
+
+// One layer through the DMA path. Host-memory accesses of a CopyStream are ordered by its DMA stream, device-memory
+// accesses by its main stream; the two meet through the staging-slot events.
+int host_dma_layer(CopyStream* cs, const void* src, void* dst, bool host_is_src, int prefix_dim, int suffix_dim,
+                   int elem_size, int src_block_dim, int dst_block_dim) {
+  HostDma& h = cs->hd;
+  const int n = cs->num_blocks;
+  const size_t chunk = (size_t)suffix_dim * (size_t)elem_size;
+  const size_t need = (size_t)prefix_dim * (size_t)n * chunk;
+  if (int rc = host_dma_prepare(cs, host_is_src, need)) return rc;
+  const int slot = h.next;
+  h.next ^= 1;
+  char* stage = (char*)h.staging[slot];
+  const std::vector<int>& host_ids = host_is_src ? cs->h_src : cs->h_dst;
+  const size_t host_prefix = (size_t)(host_is_src ? src_block_dim : dst_block_dim) * chunk;
+  if (host_is_src) {
+    // onboard: DMA the runs into staging, then one kernel scatters staging -> device blocks
+    if (h.drained_valid[slot]) KVDP_CUDA(cudaStreamWaitEvent(h.dma, h.drained[slot], 0));
+    for (int p = 0; p < prefix_dim; ++p)
+      for (size_t r = 0; r < h.run_pos.size(); ++r)
+        KVDP_CUDA(cudaMemcpyAsync(stage + ((size_t)p * n + h.run_pos[r]) * chunk,
+                                  (const char*)src + p * host_prefix + (size_t)host_ids[h.order[h.run_pos[r]]] * chunk,
+                                  (size_t)h.run_len[r] * chunk, cudaMemcpyHostToDevice, h.dma));
+    KVDP_CUDA(cudaEventRecord(h.filled[slot], h.dma));
+    KVDP_CUDA(cudaStreamWaitEvent(cs->stream, h.filled[slot], 0));
+    if (int rc = launch_3d(stage, dst, h.ids.d_src(), h.ids.d_dst(), n, prefix_dim, suffix_dim, elem_size, n,
+                           dst_block_dim, false, cs->stream))
+      return rc;
+    KVDP_CUDA(cudaEventRecord(h.drained[slot], cs->stream));
+    h.drained_valid[slot] = true;
+    return h.ids.mark_in_use(cs->stream);
+  }
+  // offload: one kernel gathers device blocks -> staging (host-sorted order), then DMA the runs out
+  if (h.drained_valid[slot]) KVDP_CUDA(cudaStreamWaitEvent(cs->stream, h.drained[slot], 0));
+  if (int rc = launch_3d(src, stage, h.ids.d_src(), h.ids.d_dst(), n, prefix_dim, suffix_dim, elem_size, src_block_dim,
+                         n, false, cs->stream))
+    return rc;
+  KVDP_CUDA(cudaEventRecord(h.filled[slot], cs->stream));
+  if (int rc = h.ids.mark_in_use(cs->stream)) return rc;
+  KVDP_CUDA(cudaStreamWaitEvent(h.dma, h.filled[slot], 0));
+  for (int p = 0; p < prefix_dim; ++p)
+    for (size_t r = 0; r < h.run_pos.size(); ++r)
+      KVDP_CUDA(cudaMemcpyAsync((char*)dst + p * host_prefix + (size_t)host_ids[h.order[h.run_pos[r]]] * chunk,
+                                stage + ((size_t)p * n + h.run_pos[r]) * chunk, (size_t)h.run_len[r] * chunk,
+                                cudaMemcpyDeviceToHost, h.dma));
+  KVDP_CUDA(cudaEventRecord(h.drained[slot], h.dma));
+  h.drained_valid[slot] = true;
+  KVDP_CUDA(cudaEventRecord(h.tail, h.dma));
+  h.tail_valid = true;
+  return 0;
+}
+
 // Process-wide id staging for the handle-less entry points (copy_blocks_3d / copy_blocks_memcpy_3d), one per device.
 struct GlobalStage {
   std::mutex mu;
@@ -203,6 +363,7 @@ int copy_stream_destroy(CopyStream* cs) {
   if (!cs) return 0;
   DeviceGuard g(cs->device);
   if (cs->stream) cudaStreamSynchronize(cs->stream);
+  host_dma_destroy(cs->hd);
   cs->ids.destroy();
   if (cs->stream) cudaStreamDestroy(cs->stream);
   delete cs;
@@ -217,6 +378,7 @@ int copy_stream_prepare_block_ids(CopyStream* cs, int* src_block_ids, int* dst_b
   cs->h_src.assign(src_block_ids, src_block_ids + num_blocks);
   cs->h_dst.assign(dst_block_ids, dst_block_ids + num_blocks);
   cs->num_blocks = num_blocks;
+  cs->hd.sorted_for = 0;
   if (num_blocks == 0) return 0;
   return cs->ids.upload(src_block_ids, dst_block_ids, num_blocks, cs->stream);
 }
@@ -244,6 +406,15 @@ int copy_stream_memcpy(CopyStream* cs, const void* src_data, void* dst_data, int
       (uint64_t)suffix_dim * (uint64_t)elem_size >= ((uint64_t)1 << 32))
     return dma_loop_3d(src_data, dst_data, cs->h_src.data(), cs->h_dst.data(), cs->num_blocks, prefix_dim,
                        suffix_dim, elem_size, src_block_dim, dst_block_dim, cs->stream);
+  // exactly one side in pinned host memory and long consecutive runs on that side: copy engines + one kernel
+  if ((sk == kPinned) != (dk == kPinned) && options().host_path == 0 &&
+      host_dma_plan(cs, sk == kPinned, (size_t)suffix_dim * (size_t)elem_size))
+    return host_dma_layer(cs, src_data, dst_data, sk == kPinned, prefix_dim, suffix_dim, elem_size, src_block_dim,
+                          dst_block_dim);
+  if (host && cs->hd.tail_valid) {  // an earlier offload of this handle may still be writing host memory
+    KVDP_CUDA(cudaStreamWaitEvent(cs->stream, cs->hd.tail, 0));
+    cs->hd.tail_valid = false;
+  }
   if (int rc = launch_3d(src_data, dst_data, cs->ids.d_src(), cs->ids.d_dst(), cs->num_blocks, prefix_dim,
                          suffix_dim, elem_size, src_block_dim, dst_block_dim, host, cs->stream))
     return rc;
@@ -254,6 +425,8 @@ int copy_stream_sync(CopyStream* cs) {
   if (!cs || !cs->stream) return fail((int)cudaErrorInvalidValue, "copy_stream_sync: unusable handle");
   DeviceGuard g(cs->device);
   KVDP_CUDA(cudaStreamSynchronize(cs->stream));
+  if (cs->hd.dma) KVDP_CUDA(cudaStreamSynchronize(cs->hd.dma));  // offloads finish on the DMA stream
+  cs->hd.tail_valid = false;
   return 0;
 }
 

@@ -21,6 +21,7 @@ int IdStage::init(int max_pairs, int dev) {
     KVDP_CUDA(cudaMalloc(&d_slot[s], sizeof(int32_t) * 2 * (size_t)capacity));
     KVDP_CUDA(cudaHostAlloc(&h_slot[s], sizeof(int32_t) * 2 * (size_t)capacity, cudaHostAllocDefault));
     KVDP_CUDA(cudaEventCreateWithFlags(&ev[s], cudaEventDisableTiming));
+    slot_cap[s] = capacity;
     used[s] = false;
   }
   KVDP_CUDA(cudaMalloc(&d_counter, sizeof(unsigned int)));
@@ -51,14 +52,22 @@ void IdStage::destroy() {
 
 int IdStage::upload(const int32_t* h_src, const int32_t* h_dst, int n, cudaStream_t stream) {
   if (!ok) return fail(KVDP_ESTATE, "id staging was not initialised (allocation failed at create time)");
-  if (n > capacity) {
-    // rare: the caller exceeds the size it announced. Drain and reallocate (destroy() waits on every slot).
-    const int dev = device, cap = std::max(n, capacity * 2);
-    destroy();
-    if (int rc = init(cap, dev)) return rc;
-  }
   const int s = (cur + 1) % kSlots;
   if (used[s]) KVDP_CUDA(cudaEventSynchronize(ev[s]));  // the kernel that last read this slot has finished
+  if (n > slot_cap[s]) {
+    // rare: the caller exceeds the size it announced. Only this slot grows (its last reader is done, see above); the
+    // other slots, which may still be in flight, are left alone and grow when their turn comes.
+    DeviceGuard g(device);
+    capacity = std::max(capacity, std::max(n, slot_cap[s] * 2));
+    KVDP_CUDA(cudaFree(d_slot[s]));
+    d_slot[s] = nullptr;
+    KVDP_CUDA(cudaFreeHost(h_slot[s]));
+    h_slot[s] = nullptr;
+    slot_cap[s] = 0;
+    KVDP_CUDA(cudaMalloc(&d_slot[s], sizeof(int32_t) * 2 * (size_t)capacity));
+    KVDP_CUDA(cudaHostAlloc(&h_slot[s], sizeof(int32_t) * 2 * (size_t)capacity, cudaHostAllocDefault));
+    slot_cap[s] = capacity;
+  }
   memcpy(h_slot[s], h_src, sizeof(int32_t) * (size_t)n);
   memcpy(h_slot[s] + n, h_dst, sizeof(int32_t) * (size_t)n);
   KVDP_CUDA(cudaMemcpyAsync(d_slot[s], h_slot[s], sizeof(int32_t) * 2 * (size_t)n, cudaMemcpyHostToDevice, stream));

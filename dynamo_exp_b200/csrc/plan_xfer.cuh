@@ -13,6 +13,7 @@ struct IdStage {
   int32_t* h_slot[kSlots] = {};
   int32_t* d_slot[kSlots] = {};
   cudaEvent_t ev[kSlots] = {};
+  int slot_cap[kSlots] = {};  // pairs each slot can hold (slots grow one at a time, when their last reader is done)
   bool used[kSlots] = {};
   unsigned int* d_counter = nullptr;  // CTA arrival counter for the in-kernel completion flag
   int capacity = 0;

@@ -95,7 +95,7 @@ int kvdp_set_option(const char* name, int64_t value) {
     if (value < 0 || value > 32) return fail(KVDP_EINVAL, "ctas_per_sm must be 0..32");
     o.ctas_per_sm = value;
   } else if (!strcmp(name, "host_path")) {
-    if (value < 0 || value > 2) return fail(KVDP_EINVAL, "host_path must be 0, 1 or 2");
+    if (value < 0 || value > 3) return fail(KVDP_EINVAL, "host_path must be 0..3");
     o.host_path = value;
   } else if (!strcmp(name, "l2_hint")) {
     if (value < 0 || value > 3) return fail(KVDP_EINVAL, "l2_hint must be 0..3");

@@ -793,7 +793,8 @@ int hash_token_blocks_impl(const uint32_t* d_tokens, const int64_t* d_offsets, i
   // on a side stream under the block hashing of range k+1 and is joined back onto the caller's stream at the end, so
   // the caller sees one ordered call. Only the last range's chain is not hidden.
   int stages = (int)options().hash_stages;
-  if (stages <= 0) stages = 4;
+  if (stages <= 0) stages = 1;  // measured (profiles/sweep_r02_hash_stages.txt): every extra range costs ~16 us of
+                                // launch ramp and tail and its chain still pays the serial floor; off by default
   stages = std::min(stages, kMaxHashStages);
   const bool staged = may_fork && d_seq_hash && stages > 1 && dev >= 0 && dev < 64 && n_req >= 4096 &&
                       (int64_t)max_blocks * block_size * 4 >= ((int64_t)64 << 20);
@@ -895,10 +896,11 @@ int ensure(void** p, size_t* cap, size_t need) {
   return 0;
 }
 
-constexpr int64_t kHostChunkTokens = (int64_t)1 << 20;  // 4 MiB of tokens per pipeline step
+constexpr int64_t kHostChunkTokens = (int64_t)4 << 20;  // 16 MiB of tokens per pipeline step: with 4 MiB pieces the gaps
+                                                        // between consecutive DMAs cost ~10 % of the link
 }  // namespace
 
-// Upload, hashing and download overlap: the batch is cut at request boundaries into pieces of about 4 MiB of tokens;
+// Upload, hashing and download overlap: the batch is cut at request boundaries into pieces of about 16 MiB of tokens;
 // piece k is hashed (and chained) on the compute stream while piece k+1 is still on its way up and the results of piece
 // k-1 are on their way down, each on a stream of its own. With pinned host buffers the call runs at the speed of the
 // host->device link; pageable buffers work too (the driver stages them).

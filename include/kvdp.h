@@ -43,10 +43,14 @@ const char* kvdp_last_error(void);
 int kvdp_version(void);
 /* tunables: "copy_path" (0 auto, 1 vector ld/st, 2 TMA-load + vector store, 3 TMA load + TMA store, 4 warp-per-chunk
  * vectors for chunks <= 4 KiB),
- * "tile_bytes", "stages", "ctas_per_sm", "host_path" (pinned memory: 0 vector kernel, 1 DMA loop, 2 TMA kernel), "host_ctas", "l2_hint",
+ * "tile_bytes", "stages", "ctas_per_sm", "host_path" (pinned memory: 0 auto = a CopyStream whose
+ * host-side ids form runs of >= 1 MiB on average moves them with one DMA per run through an HBM staging buffer plus one
+ * kernel, anything else uses the vector kernel; 1 per-chunk DMA loop as the reference does; 2 TMA kernel; 3 vector
+ * kernel always), "host_ctas", "l2_hint",
  * "vec32" (copy path 1: 256-bit loads/stores when every pointer and stride is 32-byte aligned; +5 % on that path in HBM,
  * no change over NVLink), "hash_stages" (chained hashing of a big batch: number of request ranges whose chain kernels
- * run under the next range's block hashing; 0 = default 4, 1 = one range, nothing leaves the caller's stream).
+ * run under the next range's block hashing; 0 or 1 = off, the default: everything stays on the caller's stream —
+ * measured on the router batch every extra range cost more in launch ramp and tail than the overlap returned).
  * Returns KVDP_EINVAL for
  * unknown names. Intended for benchmarking; defaults are what the tests run. */
 int kvdp_set_option(const char* name, int64_t value);
@@ -243,11 +247,11 @@ int kvdp_host_tier_sync(kvdp_host_tier* t);
 #define KVDP_HASH_TWIN_FIRST 1u
 size_t kvdp_hash_workspace_bytes(int64_t n_req);
 /* all pointers are device pointers; seq_hash may be NULL (un-chained only). total_tokens = offsets[n_req] as known to
- * the host (sizes the grid). Asynchronous and ordered on `stream` like one kernel. Internally a big chained batch
- * (>= 4096 requests, >= 64 MiB of tokens) is cut into request ranges: the serial, latency-bound chain kernel of one
- * range runs on a library-owned side stream under the HBM-bound block hashing of the next range and is joined back
- * onto `stream` before the call's work counts as complete (streams and events are created on the first such call per
- * device). The result is the same bits either way. */
+ * the host (sizes the grid). Asynchronous and ordered on `stream` like one kernel. With the "hash_stages" option set
+ * above 1, a big chained batch (>= 4096 requests, >= 64 MiB of tokens) is cut into that many request ranges: the
+ * serial, latency-bound chain kernel of one range runs on a library-owned side stream under the HBM-bound block hashing
+ * of the next range and is joined back onto `stream` before the call's work counts as complete (streams and events are
+ * created on the first such call per device). The result is the same bits either way. */
 int kvdp_hash_token_blocks(const uint32_t* d_tokens, const int64_t* d_offsets, int64_t n_req, int64_t total_tokens,
                            int32_t block_size, uint64_t salt, int64_t* d_block_offsets, uint64_t* d_block_hash,
                            uint64_t* d_seq_hash, void* d_workspace, size_t workspace_bytes, uint32_t flags,

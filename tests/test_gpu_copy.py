@@ -617,3 +617,61 @@ def test_random_plan_geometries_against_the_address_algebra(gpu, seed):
                 assert np.array_equal(b.download(), w), (seed, case, path, k, desc)
         plan.close()
         eng.close()
+
+
+@pytest.mark.parametrize("host_path", [0, 3, 1])
+def test_copy_stream_coalesced_dma_host_path(gpu, oracle, host_path):
+    """Pinned-host endpoint with 128 KiB chunks whose host-side ids form long runs (two requests of 16 consecutive host
+    blocks, listed in shuffled order): host_path 0 takes the copy-engine path (one DMA per run through HBM staging + one
+    kernel), 3 the zero-copy kernel, 1 the reference's per-chunk DMA loop. Same bytes from all three, both directions,
+    and a scattered id set afterwards on the same handle (falls back to the kernel) must still be ordered behind them."""
+    from tests.util import PinnedBuf
+    L = gpu.lib()
+    gpu.set_option("host_path", host_path)
+    layers, nh, nd, suffix, elem = 3, 64, 48, 64 * 1024, 2
+    chunk = suffix * elem
+    rng = np.random.Generator(np.random.PCG64(host_path + 10))
+    host = [PinnedBuf(gpu, 2 * nh * chunk) for _ in range(layers)]
+    back = [PinnedBuf(gpu, 2 * nh * chunk) for _ in range(layers)]
+    dev = [DevBuf(gpu, 2 * nd * chunk) for _ in range(layers)]
+    src_np = []
+    for l, h in enumerate(host):
+        h.array[:] = payload(h.nbytes, 300 + l)
+        src_np.append(h.array.copy())
+    pairs = 32
+    h_ids = np.concatenate([np.arange(8, 24), np.arange(40, 56)]).astype(np.int32)
+    d_ids = rng.permutation(nd)[:pairs].astype(np.int32)
+    shuffle = rng.permutation(pairs)
+    h_ids, d_ids = h_ids[shuffle].copy(), d_ids[shuffle].copy()
+    cs = C.c_void_p()
+    assert L.copy_stream_create(C.byref(cs), layers, pairs) == 0
+    # onboard
+    assert L.copy_stream_prepare_block_ids(cs, h_ids.ctypes.data, d_ids.ctypes.data, pairs) == 0
+    for l in range(layers):
+        assert L.copy_stream_memcpy(cs, host[l].ptr, dev[l].ptr, 2, suffix, elem, nh, nd) == 0, gpu.last_error()
+    assert L.copy_stream_sync(cs) == 0
+    want_dev = [np.zeros(2 * nd * chunk, dtype=np.uint8) for _ in range(layers)]
+    oracle.copy_blocks_layers(src_np, want_dev, h_ids, d_ids, 2, nh, nd, suffix, elem)
+    for l in range(layers):
+        assert np.array_equal(dev[l].download(), want_dev[l]), ("onboard", l)
+    # offload into other host blocks (runs again), twice in a row without a sync in between: the second id set reuses the
+    # staging slots and the sorted-id buffer of the first
+    h2 = np.concatenate([np.arange(0, 16), np.arange(24, 40)]).astype(np.int32)[rng.permutation(pairs)].copy()
+    want_back = [np.zeros(2 * nh * chunk, dtype=np.uint8) for _ in range(layers)]
+    for ids_h in (h2, ((h2 + 7) % nh).astype(np.int32)):
+        assert L.copy_stream_prepare_block_ids(cs, d_ids.ctypes.data, ids_h.ctypes.data, pairs) == 0
+        for l in range(layers):
+            assert L.copy_stream_memcpy(cs, dev[l].ptr, back[l].ptr, 2, suffix, elem, nd, nh) == 0, gpu.last_error()
+        oracle.copy_blocks_layers(want_dev, want_back, d_ids, ids_h, 2, nd, nh, suffix, elem)
+    # scattered ids right behind (no runs: kernel path) overwrite a few of the same host blocks
+    s_dev = rng.permutation(nd)[:6].astype(np.int32)
+    s_host = np.array([1, 9, 17, 33, 41, 63], dtype=np.int32)
+    assert L.copy_stream_prepare_block_ids(cs, s_dev.ctypes.data, s_host.ctypes.data, 6) == 0
+    for l in range(layers):
+        assert L.copy_stream_memcpy(cs, dev[l].ptr, back[l].ptr, 2, suffix, elem, nd, nh) == 0
+    oracle.copy_blocks_layers(want_dev, want_back, s_dev, s_host, 2, nd, nh, suffix, elem)
+    assert L.copy_stream_sync(cs) == 0
+    for l in range(layers):
+        assert np.array_equal(back[l].array, want_back[l]), ("offload", l)
+    assert L.copy_stream_destroy(cs) == 0
+    gpu.set_option("host_path", 0)
