@@ -16,7 +16,13 @@
 //   * find_matches runs for a whole batch of requests in one launch, one thread per request, each step ONE 32-byte
 //     dependent random read; per-worker scores are kept as bit-sliced counters (one 64-bit plane per
 //     binary digit), so adding a node's worker set costs a ripple of AND/XORs instead of a 64-way loop.
-// Up to 64 workers per index (one bitset word); the host layer maps WorkerId -> slot.
+// Worker sets: up to 64 workers fit the 64-bit word an edge record carries (one dependent read per step). An index
+// created for more (up to 512) keeps ceil(W/64) words per node in a second, node-indexed device table: the edge then
+// carries the child's worker COUNT (for the early exit), one thread walks a request once per 64-worker word (grid.y)
+// and reads that word of the child's set next to the edge it follows — two reads per step that do not depend on each
+// other. The reference's set is an unbounded HashSet<WorkerId> (indexer.rs:163-170); the host layer maps WorkerId -> slot.
+// Nodes are reference-counted by their incoming parent edges and per-worker lookup entries, as the reference's
+// Rc<RefCell<RadixBlock>> are: a subtree dropped by "last worker left" is reclaimed and its ids are reused.
 #include <string.h>
 
 #include <algorithm>
@@ -51,16 +57,22 @@ __host__ __device__ __forceinline__ uint64_t edge_slot_hash(uint64_t hash, uint3
 }
 
 constexpr int kPlanes = 16;  // bit-sliced counters: depths up to 65535 blocks
+constexpr int kMaxWorkerWords = 8;  // 512 workers per index
 
+// MULTI = false: worker sets of <= 64 workers ride in the edge record. MULTI = true: blockIdx.y selects a 64-worker word
+// of the node-indexed set table `wsets` ([node][words]); the edge's worker field then holds the child's worker count.
+template <bool MULTI>
 __global__ void __launch_bounds__(128) kvdp_index_find_kernel(const EdgeRec* __restrict__ edges, uint64_t mask,
                                                               uint32_t root_gen,
                                                               const uint64_t* __restrict__ hashes,
                                                               const int64_t* __restrict__ seq_offsets, int64_t n_req,
                                                               int early_exit, int num_workers,
                                                               uint32_t* __restrict__ scores,
-                                                              int32_t* __restrict__ matched_depth) {
+                                                              int32_t* __restrict__ matched_depth,
+                                                              const uint64_t* __restrict__ wsets, int words) {
   const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= n_req) return;
+  const int word = MULTI ? (int)blockIdx.y : 0;
   const int64_t s0 = seq_offsets[r], s1 = seq_offsets[r + 1];
   uint64_t plane[kPlanes];
 #pragma unroll
@@ -84,8 +96,15 @@ __global__ void __launch_bounds__(128) kvdp_index_find_kernel(const EdgeRec* __r
       slot = (slot + 1) & mask;
     }
     if (!found) break;
-    uint64_t carry = (uint64_t)b.x | ((uint64_t)b.y << 32);
-    const int nworkers = __popcll(carry);
+    uint64_t carry;
+    int nworkers;
+    if (MULTI) {
+      carry = __ldg(wsets + (size_t)b.z * (size_t)words + word);     // independent of the next edge read
+      nworkers = (int)b.x;
+    } else {
+      carry = (uint64_t)b.x | ((uint64_t)b.y << 32);
+      nworkers = __popcll(carry);
+    }
     ++depth;
 #pragma unroll
     for (int p = 0; p < kPlanes; ++p) {   // planes += worker mask
@@ -97,13 +116,21 @@ __global__ void __launch_bounds__(128) kvdp_index_find_kernel(const EdgeRec* __r
     node = b.z;
     gen = b.w - 1;
   }
-  if (matched_depth) matched_depth[r] = depth;
-  for (int w = 0; w < num_workers; ++w) {
+  if (matched_depth && word == 0) matched_depth[r] = depth;
+  const int w_end = min(num_workers - word * 64, 64);
+  for (int w = 0; w < w_end; ++w) {
     uint32_t c = 0;
 #pragma unroll
     for (int p = 0; p < kPlanes; ++p) c |= (uint32_t)((plane[p] >> w) & 1ULL) << p;
-    scores[r * (int64_t)num_workers + w] = c;
+    scores[r * (int64_t)num_workers + word * 64 + w] = c;
   }
+}
+
+// table[idx[i]][0..words) = recs[i][0..words): worker-set words of the nodes whose sets changed
+__global__ void kvdp_index_scatter_words_kernel(uint64_t* __restrict__ table, const uint32_t* __restrict__ idx,
+                                                const uint64_t* __restrict__ recs, int n, int words) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n * words) table[(size_t)idx[i / words] * words + i % words] = recs[i];
 }
 
 template <typename Rec>
@@ -116,9 +143,24 @@ __global__ void kvdp_index_scatter_kernel(Rec* __restrict__ table, const uint32_
 struct HostNode {
   std::unordered_map<uint64_t, uint32_t> children;  // tokens hash -> node id
   std::vector<uint32_t> in_slots;                    // edge-table slots of edges that point at this node
-  uint64_t workers = 0;
+  uint64_t workers[kMaxWorkerWords] = {};
   uint32_t gen = 0;
+  uint32_t refs = 0;  // parent edges + per-worker lookup entries that name this node (the reference's Rc count)
   std::deque<int64_t> recent_uses;  // access times (ns) inside the expiration window; only kept when tracking is on
+
+  bool has(int w) const { return workers[w >> 6] >> (w & 63) & 1ULL; }
+  void add(int w) { workers[w >> 6] |= 1ULL << (w & 63); }
+  void drop(int w) { workers[w >> 6] &= ~(1ULL << (w & 63)); }
+  int count() const {
+    int c = 0;
+    for (int k = 0; k < kMaxWorkerWords; ++k) c += __builtin_popcountll(workers[k]);
+    return c;
+  }
+  bool none() const {
+    for (int k = 0; k < kMaxWorkerWords; ++k)
+      if (workers[k]) return false;
+    return true;
+  }
 };
 
 }  // namespace
@@ -132,10 +174,15 @@ struct kvdp_index {
   int64_t max_nodes = 0;
   uint64_t capacity = 0;  // edge table slots (power of two)
   uint64_t live_slots = 0;
+  int words = 1;          // 64-bit words per worker set (1: sets ride in the edge records)
   std::vector<HostNode> nodes;
-  std::unordered_map<uint64_t, uint32_t> lookup[64];
-  bool lookup_present[64] = {};
-  int64_t member_nodes[64] = {};  // nodes whose worker set holds this slot (0 after remove_worker = slot reusable)
+  std::vector<uint32_t> free_nodes;  // reclaimed node ids
+  std::vector<std::unordered_map<uint64_t, uint32_t>> lookup;  // [worker slot]: engine block hash -> node
+  std::vector<uint8_t> lookup_present;
+  std::vector<int64_t> member_nodes;  // nodes whose worker set holds this slot (0 after remove_worker = slot reusable)
+  uint64_t* d_wsets = nullptr;        // words > 1: [max_nodes][words]
+  std::vector<uint32_t> dirty_nodes;
+  std::vector<uint8_t> node_dirty_flag;
   std::vector<EdgeRec> h_edges;
   EdgeRec* d_edges = nullptr;
   std::vector<uint32_t> dirty_edges;
@@ -163,15 +210,23 @@ void mark_edge(kvdp_index* ix, uint64_t slot) {
 }
 
 // A node's worker set or generation changed: refresh the copies carried by its incoming edges.
+uint64_t edge_worker_field(const kvdp_index* ix, const HostNode& h) {
+  return ix->words == 1 ? h.workers[0] : (uint64_t)h.count();
+}
+
 void mark_node(kvdp_index* ix, uint32_t n) {
   const HostNode& h = ix->nodes[n];
   for (uint32_t slot : h.in_slots) {
     EdgeRec& e = ix->h_edges[slot];
     if (e.child_gen1 != 0 && e.child == n) {
-      e.child_workers = h.workers;
+      e.child_workers = edge_worker_field(ix, h);
       e.child_gen1 = h.gen + 1;
       mark_edge(ix, slot);
     }
+  }
+  if (ix->words > 1 && !ix->node_dirty_flag[n]) {
+    ix->node_dirty_flag[n] = 1;
+    ix->dirty_nodes.push_back(n);
   }
 }
 
@@ -186,7 +241,7 @@ int insert_edge(kvdp_index* ix, uint32_t parent, uint64_t hash, uint32_t child) 
       e.parent = parent;
       e.gen = gen;
       e.child = child;
-      e.child_workers = ix->nodes[child].workers;
+      e.child_workers = edge_worker_field(ix, ix->nodes[child]);
       e.child_gen1 = ix->nodes[child].gen + 1;
       ++ix->live_slots;
       ix->nodes[child].in_slots.push_back((uint32_t)slot);
@@ -213,11 +268,49 @@ int rebuild_edges(kvdp_index* ix) {
 }
 
 int new_node(kvdp_index* ix, uint32_t* out) {
+  if (!ix->free_nodes.empty()) {  // a reclaimed id: its generation kept counting, so none of its old edges match
+    *out = ix->free_nodes.back();
+    ix->free_nodes.pop_back();
+    return 0;
+  }
   if ((int64_t)ix->nodes.size() >= ix->max_nodes)
-    return fail(KVDP_ERANGE, "prefix index: node capacity %lld exhausted", (long long)ix->max_nodes);
+    return fail(KVDP_ERANGE, "prefix index: node capacity %lld exhausted (live nodes)", (long long)ix->max_nodes);
   ix->nodes.emplace_back();
+  if (ix->words > 1) ix->node_dirty_flag.push_back(0);
   *out = (uint32_t)ix->nodes.size() - 1;
   return 0;
+}
+
+// One reference to node `n` went away (a parent dropped its children, or a lookup entry was removed / replaced). At
+// zero the node is gone for good, like an Rc: its own children lose a reference each, and its id goes on the free list.
+void release_node(kvdp_index* ix, uint32_t first) {
+  std::vector<uint32_t> work{first};
+  while (!work.empty()) {
+    const uint32_t n = work.back();
+    work.pop_back();
+    HostNode& h = ix->nodes[n];
+    if (n == 0 || h.refs == 0 || --h.refs != 0) continue;
+    for (auto& kv : h.children) work.push_back(kv.second);
+    h.children.clear();
+    ++h.gen;  // edges out of this id (device side) stop matching, also after the id is reused
+    for (int w = 0; w < ix->max_workers; ++w)
+      if (h.has(w)) --ix->member_nodes[w];  // a stale membership left by remove_worker dies with the node
+    for (int k = 0; k < kMaxWorkerWords; ++k) h.workers[k] = 0;
+    h.in_slots.clear();  // the edges that pointed here belong to dropped generations of their parents
+    h.recent_uses.clear();
+    ix->free_nodes.push_back(n);
+  }
+}
+
+// Node `n` lost its last worker: none of its descendants is held through it any more (indexer.rs:366-369).
+void drop_children(kvdp_index* ix, uint32_t n) {
+  HostNode& h = ix->nodes[n];
+  std::vector<uint32_t> kids;
+  kids.reserve(h.children.size());
+  for (auto& kv : h.children) kids.push_back(kv.second);
+  h.children.clear();
+  ++h.gen;  // device side: every edge out of this node stops matching
+  for (uint32_t c : kids) release_node(ix, c);
 }
 
 int ensure_stage(kvdp_index* ix, size_t n) {
@@ -242,11 +335,16 @@ int kvdp_index_create(kvdp_index** out, int64_t max_nodes, int32_t max_workers, 
   if (!out) return fail(KVDP_EINVAL, "kvdp_index_create: NULL out");
   *out = nullptr;
   if (max_nodes < 2 || max_nodes > ((int64_t)1 << 31)) return fail(KVDP_EINVAL, "prefix index: max_nodes out of range");
-  if (max_workers < 1 || max_workers > 64) return fail(KVDP_EINVAL, "prefix index: max_workers must be 1..64");
+  if (max_workers < 1 || max_workers > 64 * kMaxWorkerWords)
+    return fail(KVDP_EINVAL, "prefix index: max_workers must be 1..%d", 64 * kMaxWorkerWords);
   kvdp_index* ix = new kvdp_index();
   ix->device = device;
   if (ix->device < 0) cudaGetDevice(&ix->device);
   ix->max_workers = max_workers;
+  ix->words = (max_workers + 63) / 64;
+  ix->lookup.resize(max_workers);
+  ix->lookup_present.assign(max_workers, 0);
+  ix->member_nodes.assign(max_workers, 0);
   ix->max_nodes = max_nodes;
   uint64_t cap = 1024;
   while (cap < (uint64_t)max_nodes * 4) cap <<= 1;  // load factor <= 0.25 for live edges, room for dead generations
@@ -255,10 +353,17 @@ int kvdp_index_create(kvdp_index** out, int64_t max_nodes, int32_t max_workers, 
   ix->edge_dirty_flag.assign(cap, 0);
   ix->nodes.reserve((size_t)std::min<int64_t>(max_nodes, 1 << 20));
   ix->nodes.emplace_back();  // root
+  ix->nodes[0].refs = 1;     // never released
+  if (ix->words > 1) ix->node_dirty_flag.push_back(0);
   DeviceGuard g(ix->device);
   cudaError_t e = cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaMalloc(&ix->d_edges, sizeof(EdgeRec) * cap);
   if (e == cudaSuccess) e = cudaMemset(ix->d_edges, 0, sizeof(EdgeRec) * cap);
+  if (e == cudaSuccess && ix->words > 1) {
+    const size_t bytes = sizeof(uint64_t) * (size_t)max_nodes * (size_t)ix->words;
+    e = cudaMalloc(&ix->d_wsets, bytes);
+    if (e == cudaSuccess) e = cudaMemset(ix->d_wsets, 0, bytes);
+  }
   if (e != cudaSuccess) {
     kvdp_index_destroy(ix);
     return fail((int)e, "prefix index: device allocation failed: %s", cudaGetErrorString(e));
@@ -277,6 +382,7 @@ int kvdp_index_destroy(kvdp_index* ix) {
     cudaStreamDestroy(ix->stream);
   }
   if (ix->d_edges) cudaFree(ix->d_edges);
+  if (ix->d_wsets) cudaFree(ix->d_wsets);
   if (ix->d_idx) cudaFree(ix->d_idx);
   if (ix->d_recs) cudaFree(ix->d_recs);
   if (ix->d_io) cudaFree(ix->d_io);
@@ -318,15 +424,25 @@ int kvdp_index_apply_stored(kvdp_index* ix, int32_t worker, int32_t has_parent, 
         return rc;
       }
       ix->nodes[current].children.emplace(tokens_hashes[i], block);
+      ++ix->nodes[block].refs;
       if (int rc = insert_edge(ix, current, tokens_hashes[i], block)) return rc;
     }
     HostNode& b = ix->nodes[block];
-    if (!(b.workers >> worker & 1ULL)) {
-      b.workers |= 1ULL << worker;
+    if (!b.has(worker)) {
+      b.add(worker);
       ++ix->member_nodes[worker];
       mark_node(ix, block);
     }
-    lk[block_hashes[i]] = block;
+    auto prev = lk.find(block_hashes[i]);
+    if (prev == lk.end()) {
+      lk.emplace(block_hashes[i], block);
+      ++ix->nodes[block].refs;
+    } else if (prev->second != block) {  // the engine reuses a block id for other content: the old node loses this entry
+      const uint32_t old = prev->second;
+      prev->second = block;
+      ++ix->nodes[block].refs;
+      release_node(ix, old);
+    }
     current = block;
   }
   return 0;
@@ -343,15 +459,16 @@ int kvdp_index_apply_removed(kvdp_index* ix, int32_t worker, const uint64_t* blo
   for (int32_t i = 0; i < n; ++i) {
     auto it = lk.find(block_hashes[i]);
     if (it == lk.end()) continue;  // "Failed to find block to remove; skipping remove operation"
-    HostNode& b = ix->nodes[it->second];
-    if (b.workers >> worker & 1ULL) --ix->member_nodes[worker];
-    b.workers &= ~(1ULL << worker);
-    if (b.workers == 0) {
-      b.children.clear();  // no worker holds this block, so none holds its descendants through it
-      ++b.gen;             // device side: every edge out of this node stops matching
+    const uint32_t n = it->second;
+    {
+      HostNode& b = ix->nodes[n];
+      if (b.has(worker)) --ix->member_nodes[worker];
+      b.drop(worker);
     }
-    mark_node(ix, it->second);
+    if (ix->nodes[n].none()) drop_children(ix, n);  // no worker holds this block, so none holds its descendants through it
+    mark_node(ix, n);
     lk.erase(it);
+    release_node(ix, n);
   }
   return 0;
 }
@@ -362,16 +479,20 @@ int kvdp_index_remove_worker(kvdp_index* ix, int32_t worker) {
   std::lock_guard<std::recursive_mutex> guard(ix->mu);
   if (worker < 0 || worker >= ix->max_workers) return fail(KVDP_EINVAL, "prefix index: worker slot %d out of range", worker);
   if (!ix->lookup_present[worker]) return 0;
+  std::vector<uint32_t> held;
+  held.reserve(ix->lookup[worker].size());
   for (auto& kv : ix->lookup[worker]) {
     HostNode& b = ix->nodes[kv.second];
-    if (b.workers >> worker & 1ULL) {
-      b.workers &= ~(1ULL << worker);
+    if (b.has(worker)) {
+      b.drop(worker);
       --ix->member_nodes[worker];
       mark_node(ix, kv.second);
     }
+    held.push_back(kv.second);
   }
   ix->lookup[worker].clear();
   ix->lookup_present[worker] = false;
+  for (uint32_t n : held) release_node(ix, n);  // the table's references are gone (the blocks stay in the tree)
   return 0;
 }
 
@@ -387,6 +508,21 @@ int kvdp_index_flush(kvdp_index* ix) {
     for (uint32_t s : ix->dirty_edges) ix->edge_dirty_flag[s] = 0;
     ix->dirty_edges.clear();
     ix->full_upload_needed = false;
+  }
+  if (ix->words > 1 && !ix->dirty_nodes.empty()) {
+    const size_t nn = ix->dirty_nodes.size();
+    if (int rc = ensure_stage(ix, nn * (size_t)ix->words)) return rc;  // d_recs holds 32 bytes per staged entry
+    std::vector<uint64_t> sets(nn * (size_t)ix->words);
+    for (size_t i = 0; i < nn; ++i)
+      for (int k = 0; k < ix->words; ++k) sets[i * ix->words + k] = ix->nodes[ix->dirty_nodes[i]].workers[k];
+    KVDP_CUDA(cudaMemcpyAsync(ix->d_idx, ix->dirty_nodes.data(), nn * sizeof(uint32_t), cudaMemcpyHostToDevice, ix->stream));
+    KVDP_CUDA(cudaMemcpyAsync(ix->d_recs, sets.data(), sets.size() * sizeof(uint64_t), cudaMemcpyHostToDevice, ix->stream));
+    kvdp_index_scatter_words_kernel<<<(unsigned)((sets.size() + 255) / 256), 256, 0, ix->stream>>>(
+        ix->d_wsets, ix->d_idx, (const uint64_t*)ix->d_recs, (int)nn, ix->words);
+    KVDP_CUDA(cudaStreamSynchronize(ix->stream));
+    for (uint32_t n : ix->dirty_nodes) ix->node_dirty_flag[n] = 0;
+    ix->dirty_nodes.clear();
+    KVDP_CUDA(cudaGetLastError());
   }
   const size_t ne = ix->dirty_edges.size();
   if (ne == 0) return 0;
@@ -419,9 +555,15 @@ int kvdp_index_find_matches(kvdp_index* ix, const uint64_t* d_hashes, const int6
   if (int rc = kvdp_index_flush(ix)) return rc;
   DeviceGuard g(ix->device);
   cudaStream_t stream = stream_ ? (cudaStream_t)stream_ : ix->stream;
-  kvdp_index_find_kernel<<<(unsigned)((n_req + 127) / 128), 128, 0, stream>>>(
-      ix->d_edges, ix->capacity - 1, ix->nodes[0].gen, d_hashes, d_seq_offsets, n_req, early_exit, num_workers, d_scores,
-      d_matched_depth);
+  const dim3 grid((unsigned)((n_req + 127) / 128), (unsigned)(ix->words > 1 ? (num_workers + 63) / 64 : 1));
+  if (ix->words > 1)
+    kvdp_index_find_kernel<true><<<grid, 128, 0, stream>>>(ix->d_edges, ix->capacity - 1, ix->nodes[0].gen, d_hashes,
+                                                           d_seq_offsets, n_req, early_exit, num_workers, d_scores,
+                                                           d_matched_depth, ix->d_wsets, ix->words);
+  else
+    kvdp_index_find_kernel<false><<<grid, 128, 0, stream>>>(ix->d_edges, ix->capacity - 1, ix->nodes[0].gen, d_hashes,
+                                                            d_seq_offsets, n_req, early_exit, num_workers, d_scores,
+                                                            d_matched_depth, nullptr, 1);
   KVDP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -545,7 +687,7 @@ int64_t kvdp_index_touch(kvdp_index* ix, const uint64_t* h_hashes, int64_t n, in
     while (!b.recent_uses.empty() && now_ns - b.recent_uses.front() > expiration_ns) b.recent_uses.pop_front();
     if (!b.recent_uses.empty()) h_frequencies[written++] = (uint64_t)b.recent_uses.size();
     b.recent_uses.push_back(now_ns);
-    if (early_exit && __builtin_popcountll(b.workers) == 1) break;
+    if (early_exit && b.count() == 1) break;
     current = it->second;
   }
   return written;
@@ -559,20 +701,21 @@ int64_t kvdp_index_stat(kvdp_index* ix, int32_t what, uint64_t arg) {
   if (!ix) return -1;
   std::lock_guard<std::recursive_mutex> guard(ix->mu);
   switch (what) {
-    case 0: return (int64_t)ix->nodes.size();
+    case 0: return (int64_t)(ix->nodes.size() - ix->free_nodes.size());
     case 1: return arg < ix->nodes.size() ? (int64_t)ix->nodes[arg].children.size() : -1;
-    case 2: return arg < 64 ? (int64_t)ix->lookup[arg].size() : -1;
-    case 3: return arg < ix->nodes.size() ? (int64_t)__builtin_popcountll(ix->nodes[arg].workers) : -1;
+    case 2: return arg < (uint64_t)ix->max_workers ? (int64_t)ix->lookup[arg].size() : -1;
+    case 3: return arg < ix->nodes.size() ? (int64_t)ix->nodes[arg].count() : -1;
     case 4: {
       auto it = ix->nodes[0].children.find(arg);
       return it == ix->nodes[0].children.end() ? -1 : (int64_t)it->second;
     }
     case 5: {
       int64_t c = 0;
-      for (int w = 0; w < 64; ++w) c += ix->lookup_present[w] ? 1 : 0;
+      for (int w = 0; w < ix->max_workers; ++w) c += ix->lookup_present[w] ? 1 : 0;
       return c;
     }
-    case 6: return arg < 64 ? ix->member_nodes[arg] : -1;
+    case 6: return arg < (uint64_t)ix->max_workers ? ix->member_nodes[arg] : -1;
+    case 7: return (int64_t)ix->free_nodes.size();
     default: return -1;
   }
 }

@@ -20,7 +20,8 @@ from .storage import KvError
 from .tokens import _as_u32
 
 WorkerId = int
-MAX_WORKERS = 64
+MAX_WORKERS = 64            # default width of one index; RadixTree(max_workers=...) goes up to 512
+MAX_WORKERS_LIMIT = 512
 
 
 # ---------------------------------------------------------------------------------------------- protocol types
@@ -106,24 +107,30 @@ class OverlapScores:                     # indexer.rs:390-436
 class RadixTree:
     """reference: indexer.rs:187-387. Events are applied on the host inside libkvdp.so; lookups run on the GPU."""
 
-    def __init__(self, max_nodes: int = 1 << 20, device: int = -1, expiration_duration: Optional[float] = None):
+    def __init__(self, max_nodes: int = 1 << 20, device: int = -1, expiration_duration: Optional[float] = None,
+                 max_workers: int = MAX_WORKERS):
         """`expiration_duration` (seconds) is `RadixTree::new_with_frequency` (indexer.rs:217-223): lookups then also
-        report how often each matched block was visited inside that window."""
+        report how often each matched block was visited inside that window. `max_workers` (<= 512): how many workers
+        the index can hold at a time; up to 64 every walk step is one dependent read, above that one 64-worker word
+        of the set is read per step and pass (the reference's set is an unbounded HashSet, indexer.rs:163-170)."""
         _lib.require_gpu()
+        if not 1 <= int(max_workers) <= MAX_WORKERS_LIMIT:
+            raise KvError(f"max_workers must be 1..{MAX_WORKERS_LIMIT}")
         self.expiration_duration = expiration_duration
+        self.max_workers = int(max_workers)
         h = C.c_void_p()
-        _lib.check(_lib.lib().kvdp_index_create(C.byref(h), int(max_nodes), MAX_WORKERS, int(device)))
+        _lib.check(_lib.lib().kvdp_index_create(C.byref(h), int(max_nodes), self.max_workers, int(device)))
         self._h = h
         self._device = int(device)
         self._slot: Dict[WorkerId, int] = {}
-        self._worker_of_slot: List[Optional[WorkerId]] = [None] * MAX_WORKERS
+        self._worker_of_slot: List[Optional[WorkerId]] = [None] * self.max_workers
 
     def _slot_of(self, worker_id: WorkerId, create: bool) -> Optional[int]:
         s = self._slot.get(worker_id)
         if s is None and create:
             free = [i for i, w in enumerate(self._worker_of_slot) if w is None]
             if not free:
-                raise KvError(f"the prefix index holds at most {MAX_WORKERS} workers at a time (removed workers that "
+                raise KvError(f"the prefix index holds at most {self.max_workers} workers at a time (removed workers that "
                               "left stale blocks behind keep their slot)")
             s = free[0]
             self._slot[worker_id] = s
@@ -256,9 +263,9 @@ class KvIndexer:
     """reference: KvIndexer (indexer.rs:498-667) without the tokio actor: same calls, synchronous."""
 
     def __init__(self, kv_block_size: int, max_nodes: int = 1 << 20, device: int = -1,
-                 expiration_duration: Optional[float] = None):
+                 expiration_duration: Optional[float] = None, max_workers: int = MAX_WORKERS):
         self.kv_block_size = int(kv_block_size)
-        self.tree = RadixTree(max_nodes, device, expiration_duration)
+        self.tree = RadixTree(max_nodes, device, expiration_duration, max_workers)
 
     @classmethod
     def new_with_frequency(cls, expiration_duration: Optional[float], kv_block_size: int, **kw) -> "KvIndexer":
@@ -294,15 +301,15 @@ class KvIndexer:
 class KvIndexerSharded:
     """reference: KvIndexerSharded (indexer.rs:677-884): several independent radix trees, every worker bound to the
     shard that had the fewest workers when its first event arrived; a lookup asks every shard and merges the answers.
-    Here each shard is one device-resident prefix index, which also lifts the 64-worker limit of a single index to
-    64 x num_shards. Like the reference, a worker's binding is dropped by remove_worker and chosen afresh afterwards."""
+    Here each shard is one device-resident prefix index holding up to `max_workers` (<= 512) workers, so the sharded
+    indexer holds max_workers x num_shards. Like the reference, a worker's binding is dropped by remove_worker and chosen afresh afterwards."""
 
     def __init__(self, num_shards: int, kv_block_size: int, max_nodes: int = 1 << 20, device: int = -1,
-                 expiration_duration: Optional[float] = None):
+                 expiration_duration: Optional[float] = None, max_workers: int = MAX_WORKERS):
         if num_shards < 1:
             raise KvError("num_shards must be at least 1")
         self.kv_block_size = int(kv_block_size)
-        self.shards = [RadixTree(max_nodes, device, expiration_duration) for _ in range(int(num_shards))]
+        self.shards = [RadixTree(max_nodes, device, expiration_duration, max_workers) for _ in range(int(num_shards))]
         self.worker_assignments: Dict[WorkerId, int] = {}
         self.worker_counts = [0] * int(num_shards)
 

@@ -55,10 +55,12 @@ struct OverlapScores {           // indexer.rs:390-436 (frequencies: only with a
 class RadixTree {  // indexer.rs:187-387
  public:
   // `expiration_s`: RadixTree::new_with_frequency (indexer.rs:217-223); lookups then also report visit frequencies
-  explicit RadixTree(int64_t max_nodes = 1 << 20, int device = -1, std::optional<double> expiration_s = std::nullopt)
-      : expiration_s_(expiration_s) {
-    if (kvdp_index_create(&ix_, max_nodes, kMaxWorkers, device) != 0) raise(kvdp_last_error());
-    slot_worker_.assign(kMaxWorkers, std::nullopt);
+  // `max_workers` (<= 512): workers the index holds at a time (the reference's set is unbounded, indexer.rs:163-170)
+  explicit RadixTree(int64_t max_nodes = 1 << 20, int device = -1, std::optional<double> expiration_s = std::nullopt,
+                     int max_workers = 64)
+      : expiration_s_(expiration_s), max_workers_(max_workers) {
+    if (kvdp_index_create(&ix_, max_nodes, max_workers_, device) != 0) raise(kvdp_last_error());
+    slot_worker_.assign(max_workers_, std::nullopt);
   }
   ~RadixTree() { kvdp_index_destroy(ix_); }
   RadixTree(const RadixTree&) = delete;
@@ -152,18 +154,17 @@ class RadixTree {  // indexer.rs:187-387
     auto it = worker_slot_.find(w);
     if (it != worker_slot_.end()) return it->second;
     if (!create) return -1;
-    for (int s = 0; s < kMaxWorkers; ++s)
+    for (int s = 0; s < max_workers_; ++s)
       if (!slot_worker_[s]) {
         slot_worker_[s] = w;
         worker_slot_[w] = s;
         return s;
       }
-    raise("the prefix index holds at most 64 workers at a time");
+    raise("the prefix index is full: it was created for " + std::to_string(max_workers_) + " workers at a time");
     return -1;
   }
 
  private:
-  static constexpr int kMaxWorkers = 64;
   int workers_in_use() const {  // highest bound slot + 1 (at least 1): the width of the score rows
     int nw = 1;
     for (size_t s = 0; s < slot_worker_.size(); ++s)
@@ -172,6 +173,7 @@ class RadixTree {  // indexer.rs:187-387
   }
   kvdp_index* ix_ = nullptr;
   std::optional<double> expiration_s_;
+  int max_workers_ = 64;
   std::unordered_map<WorkerId, int> worker_slot_;
   std::vector<std::optional<WorkerId>> slot_worker_;
 };

@@ -181,12 +181,14 @@ def test_router_event_wire_format(gpu):
     assert RouterEvent.from_json(big.to_json()) == big
 
 
-def test_sharded_indexer_matches_sharded_oracle_with_100_workers(gpu):
+@pytest.mark.parametrize("n_shards,max_workers", [(3, 64), (1, 128), (2, 512)])
+def test_sharded_indexer_matches_sharded_oracle_with_100_workers(gpu, n_shards, max_workers):
     """KvIndexerSharded (indexer.rs:677-884): workers bound to the emptiest shard at their first event, lookups merged
-    over shards. 100 workers over 3 shards (more than one 64-slot index can hold), removals and re-binding."""
+    over shards. 100 workers over 3 shards of the default 64-worker width, over ONE index created for 128 workers (two
+    64-worker words per set) and over two of the widest (512), removals and re-binding."""
     rng = np.random.default_rng(5)
-    n_shards, n_workers = 3, 100
-    ix = KvIndexerSharded(n_shards, 16, max_nodes=1 << 14)
+    n_workers = 100
+    ix = KvIndexerSharded(n_shards, 16, max_nodes=1 << 14, max_workers=max_workers)
     ref = [OracleTree() for _ in range(n_shards)]
     assign, counts = {}, [0] * n_shards
 
@@ -230,7 +232,10 @@ def test_sharded_indexer_matches_sharded_oracle_with_100_workers(gpu):
         for t in ref:
             want.update({w: c for w, c in t.find_matches(q, False).items() if c})
         assert g.scores == want
-    assert len({w for g in got for w in g.scores}) > 64             # more workers than one index could hold
+    assert len({w for g in got for w in g.scores}) > 64             # more workers than one 64-bit set word holds
+    early = ix.shards[0].find_matches_batch(queries, True)           # early exit needs the set's total count
+    for q, g in zip(queries, early):
+        assert g.scores == {w: c for w, c in ref[0].find_matches(q, True).items() if c}
     ix.shutdown()
 
 
@@ -305,3 +310,72 @@ def test_frequency_reference_scenario_and_random_parity(gpu, num_shards):
         got = tree.find_matches(q, early, now=clock)
         assert got.scores == {w: c for w, c in want_scores.items() if c} and got.frequencies == want_freq
     tree.close()
+
+
+def test_nodes_are_reclaimed_under_churn(gpu):
+    """The reference frees a dropped subtree through Rc (indexer.rs:366-369). Here node ids come back through a free
+    list: far more distinct blocks than `max_nodes` pass through the index over time without exhausting it, lookups stay
+    right, and nothing is left behind when every worker has dropped everything."""
+    max_nodes = 256
+    trie, ref = RadixTree(max_nodes=max_nodes), OracleTree()
+    rng = np.random.default_rng(11)
+    serial = 1
+    for rnd in range(120):                               # 120 x 40 = 4 800 distinct blocks through 256 node slots
+        w = int(rng.integers(0, 3))
+        chain = list(range(serial, serial + 40))
+        serial += 40
+        blocks = [(h * 100 + w, h) for h in chain]
+        trie.apply_event(RouterEvent(w, KvCacheEvent(rnd, KvCacheStoreData(
+            None, [KvCacheStoredBlockData(b, t) for b, t in blocks]))))
+        ref.apply_stored(w, None, blocks)
+        assert trie.find_matches(chain, False).scores == {w: 40}
+        if rnd % 3 == 2:      # the head goes first: the rest hangs off a dead block, alive only through the lookup table
+            batches = [[blocks[0][0]], [b for b, _ in blocks[1:]]]
+        else:
+            batches = [[b for b, _ in reversed(blocks)]]
+        for victims in batches:
+            trie.apply_event(RouterEvent(w, KvCacheEvent(rnd, KvCacheRemoveData(victims))))
+            ref.apply_removed(w, victims)
+            assert trie.find_matches(chain, False).scores == {c_w: c for c_w, c in
+                                                              ref.find_matches(chain, False).items() if c}
+        assert trie.stat(0) <= 2                         # the root, and at most nothing else: everything was reclaimed
+    for w in range(3):
+        trie.remove_worker(w)
+        ref.remove_worker(w)
+    assert trie.stat(0) + trie.stat(7) <= max_nodes       # live + reclaimed ids never exceed what was created
+    assert trie.find_matches(list(range(1, 41)), False).scores == {}
+    # one more store after everything was dropped reuses reclaimed ids and is found
+    trie.apply_event(store_event(9, 1, [1, 2, 3]))
+    assert trie.find_matches([1, 2, 3], False).scores == {9: 3}
+
+
+def test_wide_index_random_parity_with_300_workers(gpu):
+    """An index created for 320 workers (five 64-worker words per set): random stores with shared prefixes, removals and
+    worker removals against the oracle, early exit included (it needs the total size of a node's set, which the edge
+    record carries when the set itself no longer fits in it)."""
+    rng = np.random.default_rng(21)
+    trie, ref = RadixTree(max_nodes=1 << 13, max_workers=320), OracleTree()
+    docs = [[int(x) for x in rng.integers(1, 1 << 40, size=20)] for _ in range(10)]
+    for step in range(900):
+        w = int(rng.integers(0, 300))
+        r = rng.random()
+        d = docs[int(rng.integers(0, len(docs)))]
+        if r < 0.8:
+            th = d[:int(rng.integers(1, 21))]
+            blocks = [((h ^ (w << 44)) & (2 ** 64 - 1), h) for h in th]
+            trie.apply_event(RouterEvent(w, KvCacheEvent(step, KvCacheStoreData(
+                None, [KvCacheStoredBlockData(b, t) for b, t in blocks]))))
+            ref.apply_stored(w, None, blocks)
+        elif r < 0.95:
+            victims = [(d[int(rng.integers(0, 20))] ^ (w << 44)) & (2 ** 64 - 1)]
+            trie.apply_event(RouterEvent(w, KvCacheEvent(step, KvCacheRemoveData(victims))))
+            ref.apply_removed(w, victims)
+        else:
+            trie.remove_worker(w)
+            ref.remove_worker(w)
+    queries = [d[:int(rng.integers(1, 21))] for d in docs] * 3 + [[5, 6]]
+    for early in (False, True):
+        got = trie.find_matches_batch(queries, early)
+        for q, g in zip(queries, got):
+            assert g.scores == {w: c for w, c in ref.find_matches(q, early).items() if c}, (early, q[:3])
+    assert max(len(g.scores) for g in trie.find_matches_batch(queries, False)) > 64
