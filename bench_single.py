@@ -617,7 +617,7 @@ def hash_bench(torch, lib, steps, warmup, peak):
                                         "algorithmic (ratio 1.010); profiles/ncu_full_r01_summary.txt"},
            "chained_hbm_frac": nblk * 272 / sec_serial / GB / peak}
     # e2e: pinned host tokens -> device -> hashes back on the host, through kvdp_hash_token_blocks_host
-    n_e = 7 * 256
+    n_e = 7 * 1024           # 7 168 requests, 266 MB of tokens up, 17 MB of hashes down per call
     lens_e = lens[:n_e]
     offs_e = np.zeros(n_e + 1, dtype=np.int64)
     offs_e[1:] = np.cumsum(lens_e)

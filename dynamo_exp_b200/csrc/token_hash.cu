@@ -994,8 +994,10 @@ int kvdp_hash_token_blocks_host(const uint32_t* h_tokens, const int64_t* h_offse
       KVDP_CUDA(cudaMemcpyAsync(h_seq_hash + p.b0, d_sh + p.b0, (size_t)(p.b1 - p.b0) * 8, cudaMemcpyDeviceToHost,
                                 c.down));
   }
-  KVDP_CUDA(cudaStreamSynchronize(c.up));
-  KVDP_CUDA(cudaStreamSynchronize(c.compute));
+  // the download stream is last in every dependency chain (uploads -> kernels -> downloads); a batch without any
+  // full block still has to see its uploads and the scan through
+  if (total_blocks == 0) KVDP_CUDA(cudaStreamSynchronize(c.compute));
+  KVDP_CUDA(cudaStreamSynchronize(c.up));  // trailing requests shorter than a block are uploaded but wait for nobody
   KVDP_CUDA(cudaStreamSynchronize(c.down));
   return 0;
 }
