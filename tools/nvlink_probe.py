@@ -83,6 +83,42 @@ def main():
     st = torch.cuda.Stream()
     payload = NB * LAYERS * 2 * CHUNK
     payload70 = NB * LAYERS * 2 * 64 * 2 * 128 * 2
+    if mode == "nvml":
+        # NVML's per-GPU NVLink byte counters (payload vs raw, i.e. with packet headers) around kernels AND around the copy
+        # engine, which ncu cannot see. Cumulative KiB counters, read on GPU 0 before / after a burst of each.
+        import pynvml
+        pynvml.nvmlInit()
+        h0 = pynvml.nvmlDeviceGetHandleByIndex(int(os.environ.get("CUDA_VISIBLE_DEVICES", "0").split(",")[0]))
+        ids = [pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_TX,
+               pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_RX]
+
+        def read():
+            vals = pynvml.nvmlDeviceGetFieldValues(h0, [(i, 0xFFFFFFFF) for i in ids])
+            return [int(v.value.ullVal) * 1024 for v in vals]
+        src = torch.empty(payload, dtype=torch.uint8, device="cuda:0")
+        dst = torch.empty(payload, dtype=torch.uint8, device="cuda:1")
+        print("burst                                   payload_B   data_tx_B    raw_tx_B  raw/data_tx   data_rx_B    raw_rx_B  raw/data_rx")
+        for name, fn, nbytes in (
+                ("push path 3 (bulk stores) x8", lambda: [launch(push, sid, did, st) for _ in range(8)], 8 * payload),
+                ("pull path 3 (bulk loads) x8", lambda: [launch(pull, sid, did, st) for _ in range(8)], 8 * payload),
+                ("cudaMemcpyAsync GPU0->GPU1 x8", lambda: [lib.check(L.cuda_memcpy_async(
+                    dst.data_ptr(), src.data_ptr(), payload, C.c_void_p(st.cuda_stream))) for _ in range(8)], 8 * payload),
+                ("cudaMemcpyAsync GPU1->GPU0 x8", lambda: [lib.check(L.cuda_memcpy_async(
+                    src.data_ptr(), dst.data_ptr(), payload, C.c_void_p(st.cuda_stream))) for _ in range(8)], 8 * payload)):
+            lib.set_option("copy_path", 3)
+            torch.cuda.synchronize()
+            import time
+            time.sleep(0.3)
+            b = read()
+            fn()
+            torch.cuda.synchronize()
+            time.sleep(0.3)
+            a = read()
+            d = [x - y for x, y in zip(a, b)]
+            print("%-36s %12d %11d %11d  %10.4f %11d %11d  %10.4f" %
+                  (name, nbytes, d[0], d[1], d[1] / max(d[0], 1), d[2], d[3], d[3] / max(d[2], 1)), flush=True)
+        lib.set_option("copy_path", 0)
+        return
     if mode == "launches":
         for name, plan, path, bytes_ in (("push path 3 (bulk stores)", push, 3, payload), ("pull path 3 (bulk loads)", pull, 3, payload),
                                          ("push path 1 (16-byte stores)", push, 1, payload),
