@@ -24,14 +24,28 @@ def measured_peaks():
 
 
 def ncu_traffic(kernel_key: str):
-    """Per-launch DRAM bytes of the dominant kernel from the committed ncu summary, if one exists."""
+    """Per-launch DRAM bytes of a kernel from the committed ncu capture — only while the capture still describes the
+    source this run was built from: profiles/ncu_traffic.json stores, next to each number, a hash of the kernel's source
+    files (tools/ncu_summary.py writes both); a mismatch means the kernel changed after the capture and yields None."""
     p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
-    if os.path.exists(p):
-        try:
-            return json.load(open(p)).get(kernel_key)
-        except Exception:
+    try:
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("kvdp_ncu_summary", os.path.join(ROOT, "tools", "ncu_summary.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        entry = json.load(open(p)).get(kernel_key)
+        if not isinstance(entry, dict) or entry.get("source_hash") != mod.source_hash(kernel_key):
             return None
-    return None
+        return entry["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
+def ncu_traffic_note(kernel_key: str) -> str:
+    t = ncu_traffic(kernel_key)
+    if t is None:
+        return "no ncu capture matches the current source of %s (profiles/ncu_traffic.json is keyed by a source hash)" % kernel_key
+    return "dram__bytes_read + dram__bytes_write per launch from the ncu --set full capture of this source revision"
 
 
 class Setup:
@@ -613,8 +627,7 @@ def hash_bench(torch, lib, steps, warmup, peak):
                         "frac": nblk * 264 / sec_un / GB / peak, "kernel": "kvdp_hash_blocks_tma<4,8>",
                         "algorithmic_bytes_per_launch": nblk * 264,
                         "traffic": ncu_traffic("kvdp_hash_blocks_tma"),
-                        "traffic_note": "ncu --set full on this batch: 2.150 GB read + 0.069 GB written vs 2.197 GB "
-                                        "algorithmic (ratio 1.010); profiles/ncu_full_r01_summary.txt"},
+                        "traffic_note": ncu_traffic_note("kvdp_hash_blocks_tma")},
            "chained_hbm_frac": nblk * 272 / sec_serial / GB / peak}
     # e2e: pinned host tokens -> device -> hashes back on the host, through kvdp_hash_token_blocks_host
     n_e = 7 * 1024           # 7 168 requests, 266 MB of tokens up, 17 MB of hashes down per call
@@ -664,7 +677,8 @@ def run_single(args):
         "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(args),
         "blocks_per_s": setup.pairs * args.steps / sec,
         "roofline": {"bound": "hbm", "achieved": 2 * payload / k_avg / GB, "peak": peak, "unit": "GB/s",
-                     "frac": 2 * payload / k_avg / GB / peak, "traffic": ncu_traffic(kname), "kernel": kname,
+                     "frac": 2 * payload / k_avg / GB / peak, "traffic": ncu_traffic(kname),
+                     "traffic_note": ncu_traffic_note(kname), "kernel": kname,
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": 2 * payload,
                      "avg_launch_ms": k_avg * 1e3, "best_launch_ms": k_min * 1e3,
                      "frac_of_nominal_8TBps": 2 * payload / k_avg / GB / 8000.0},
