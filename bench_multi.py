@@ -171,15 +171,17 @@ def run_multi(args, rank, local_rank, world):
                          "per_direction": pairs * BLOCK_BYTES * steps / sec / GB * max(1, P // D),
                          "verified_bytes_last_step": verified}
 
-    # ---- e2e: source blocks in pinned HOST memory on the prefill side, ONE kernel reads them over PCIe and stores
-    # them into the decode GPU's cache over NVLink (no bounce through prefill HBM); decode reads back 8 bytes.
+    # ---- e2e: a full trip with HOST buffers on both ends. Source blocks sit in pinned host memory of the prefill side;
+    # ONE kernel per step reads them over PCIe and stores them into the decode GPU's cache over NVLink (no bounce through
+    # prefill HBM) and publishes the step's completion flag there; the decode side's stream waits on that flag and copies
+    # the step's blocks out to ITS pinned host memory. Steps pipeline: step k+1 crosses NVLink while step k goes down.
     e2e = None
     if not args.no_e2e:
         import copy
         nh = 128                                      # 1 GiB of pinned blocks per prefill rank
         e_args = copy.copy(args)
         e_args.cache_blocks, e_args.requests = nh, nh // BLOCKS_PER_REQ
-        host_ptrs, e_setup = [], None
+        host_ptrs, e_setup, host_out = [], None, C.c_void_p()
         if is_prefill:
             for l in range(L8B):
                 p = C.c_void_p()
@@ -187,21 +189,60 @@ def run_multi(args, rank, local_rank, world):
                 a = np.frombuffer((C.c_uint8 * (2 * nh * CHUNK)).from_address(p.value), dtype=np.uint8)
                 a[:] = (l * 11 + rank) & 0xFF
                 host_ptrs.append(p.value)
-            e_setup = Setup(e_args, torch, lib, device=local_rank, dst_contig_ptr=peer_cache.value, dst_blocks=n,
+            # destination ids are a permutation of the first nh blocks of the decode cache: one contiguous region
+            e_setup = Setup(e_args, torch, lib, device=local_rank, dst_contig_ptr=peer_cache.value, dst_blocks=nh,
                             src_ptrs=host_ptrs)
+        else:
+            lib.check(L.cuda_malloc_host(C.byref(host_out), nh * BLOCK_BYTES))
+            C.memset(host_out.value, 0, nh * BLOCK_BYTES)
+
+        def timed_e2e(k0, count):
+            torch.cuda.synchronize()
+            dist.barrier()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            st = e_setup.stream if is_prefill else wait_stream
+            a.record(st)
+            for k in range(count):
+                seq["v"] += 1
+                if is_prefill:
+                    e_setup.step(k0 + k, done_flag=peer_flag, done_value=seq["v"])
+                else:
+                    lib.check(L.kvdp_stream_wait_flag(C.c_void_p(wait_stream.cuda_stream), flag_ptr, seq["v"]))
+                    lib.check(L.cuda_memcpy_async(host_out, own_cache, nh * BLOCK_BYTES,
+                                                  C.c_void_p(wait_stream.cuda_stream)))
+            b.record(st)
+            torch.cuda.synchronize()
+            dist.barrier()
+            t = torch.tensor([a.elapsed_time(b) / 1e3], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
         k_e = max(2, min(steps, 5))
-        timed("push", 0, 1, e_setup)
-        sec_e = timed("push", 1, k_e, e_setup)
-        result = np.zeros(8, dtype=np.uint8)
         if not is_prefill:
-            lib.check(L.cuda_memcpy_sync(result.ctypes.data, own_cache, 8))
+            lib.check(L.kvdp_memset(own_cache, 0, nh * BLOCK_BYTES))
+        timed_e2e(0, 1)
+        sec_e = timed_e2e(1, k_e)
+        bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+        if not is_prefill:      # what arrived in host memory: layer l of every block is the partner's fill byte of layer l
+            got = torch.from_numpy(np.frombuffer((C.c_uint8 * (nh * BLOCK_BYTES)).from_address(host_out.value),
+                                                 dtype=np.uint8)).view(nh, L8B, 2 * CHUNK)
+            for l in range(L8B):
+                bad += int((got[:, l] != ((l * 11 + partner) & 0xFF)).sum())
+        dist.all_reduce(bad, op=dist.ReduceOp.SUM)
+        if int(bad.item()) != 0:
+            raise RuntimeError("e2e: %d bytes in decode-side host memory differ from the prefill-side host source" % int(bad.item()))
         e2e = {"value": P * nh * BLOCK_BYTES * k_e / sec_e / GB, "unit": "GB/s",
-               "h2d_bytes_per_step": P * nh * BLOCK_BYTES, "d2h_bytes_per_step": 8 * D, "steps": k_e,
-               "api": "kvdp_plan_contig over pinned host layer pointers -> peer-mapped decode cache, kvdp_xfer_run with "
-                      "in-kernel completion flag; one launch per step, PCIe-bound per prefill GPU"}
+               "h2d_bytes_per_step": P * nh * BLOCK_BYTES, "d2h_bytes_per_step": P * nh * BLOCK_BYTES, "steps": k_e,
+               "verification": "all bytes of the decode-side host buffers",
+               "api": "kvdp_plan_contig over pinned host layer pointers (prefill side) -> peer-mapped decode cache, "
+                      "kvdp_xfer_run with in-kernel completion flag; decode side: kvdp_stream_wait_flag + cuda_memcpy_async "
+                      "into pinned host memory; one launch per step, PCIe-bound per prefill GPU. Every step carries the same "
+                      "payload into the same cache region, so step k+1's stores overlapping step k's download are benign "
+                      "here; a deployment hands out distinct blocks per request"}
         for p in host_ptrs:
             L.cuda_free_host(C.c_void_p(p))
-
+        if host_out.value:
+            L.cuda_free_host(host_out)
 
     # ---- token-granular transfer over NVLink: the same memory viewed per token slot, 2 KiB rows, all
     # layers and K|V in one launch; the decode cache region is treated as 32 layer slabs of [2, n*64 slots, 2 KiB].
