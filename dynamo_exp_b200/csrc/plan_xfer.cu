@@ -55,18 +55,26 @@ int IdStage::upload(const int32_t* h_src, const int32_t* h_dst, int n, cudaStrea
   const int s = (cur + 1) % kSlots;
   if (used[s]) KVDP_CUDA(cudaEventSynchronize(ev[s]));  // the kernel that last read this slot has finished
   if (n > slot_cap[s]) {
-    // rare: the caller exceeds the size it announced. Only this slot grows (its last reader is done, see above); the
-    // other slots, which may still be in flight, are left alone and grow when their turn comes.
+    // rare: the caller exceeds the size it announced. This slot grows (its last reader is done, see above) and so does
+    // every other slot that is idle right now, so that the allocation stalls are paid once and not again on each of the
+    // next calls; slots that are still in flight are left alone and grow when their turn comes.
     DeviceGuard g(device);
     capacity = std::max(capacity, std::max(n, slot_cap[s] * 2));
-    KVDP_CUDA(cudaFree(d_slot[s]));
-    d_slot[s] = nullptr;
-    KVDP_CUDA(cudaFreeHost(h_slot[s]));
-    h_slot[s] = nullptr;
-    slot_cap[s] = 0;
-    KVDP_CUDA(cudaMalloc(&d_slot[s], sizeof(int32_t) * 2 * (size_t)capacity));
-    KVDP_CUDA(cudaHostAlloc(&h_slot[s], sizeof(int32_t) * 2 * (size_t)capacity, cudaHostAllocDefault));
-    slot_cap[s] = capacity;
+    for (int t = 0; t < kSlots; ++t) {
+      if (slot_cap[t] >= capacity) continue;
+      if (t != s && used[t] && cudaEventQuery(ev[t]) != cudaSuccess) {
+        cudaGetLastError();  // cudaErrorNotReady is not sticky, but keep the error state clean
+        continue;
+      }
+      KVDP_CUDA(cudaFree(d_slot[t]));
+      d_slot[t] = nullptr;
+      KVDP_CUDA(cudaFreeHost(h_slot[t]));
+      h_slot[t] = nullptr;
+      slot_cap[t] = 0;
+      KVDP_CUDA(cudaMalloc(&d_slot[t], sizeof(int32_t) * 2 * (size_t)capacity));
+      KVDP_CUDA(cudaHostAlloc(&h_slot[t], sizeof(int32_t) * 2 * (size_t)capacity, cudaHostAllocDefault));
+      slot_cap[t] = capacity;
+    }
   }
   memcpy(h_slot[s], h_src, sizeof(int32_t) * (size_t)n);
   memcpy(h_slot[s] + n, h_dst, sizeof(int32_t) * (size_t)n);
