@@ -67,6 +67,9 @@ def parse_args():
                     help="N>1: push = prefill-side kernel stores into the decode GPU; pull = decode-side kernel loads "
                          "from the prefill GPU; both = measure both, headline the faster")
     ap.add_argument("--no-comparators", action="store_true", help="N>1: skip the NCCL / memcpy-peer comparison legs")
+    ap.add_argument("--e2e-path", default="dma", choices=["dma", "kernel"],
+                    help="N>1 e2e leg, prefill side: dma = legacy CopyStream (copy engines into HBM staging + push kernel), "
+                         "kernel = one zero-copy kernel reading host memory")
     ap.add_argument("--no-reshard", action="store_true", help="N>1: skip the Llama-3-70B TP reshard legs (config 3)")
     ap.add_argument("--sweep", action="store_true", help="print a table of kernel variants instead of the JSON line")
     return ap.parse_args()

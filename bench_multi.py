@@ -182,31 +182,56 @@ def run_multi(args, rank, local_rank, world):
         e_args = copy.copy(args)
         e_args.cache_blocks, e_args.requests = nh, nh // BLOCKS_PER_REQ
         host_ptrs, e_setup, host_out = [], None, C.c_void_p()
+        e_path = getattr(args, "e2e_path", "dma")
+        nhc = 2 * nh                                  # host cache: twice the step's blocks
+        dst_layer_bytes = 2 * nh * CHUNK              # the first 1 GiB of the decode cache, viewed as 32 layer slabs
+        cs = C.c_void_p()
+        rng_e = np.random.Generator(np.random.PCG64(4321 + rank))
         if is_prefill:
             for l in range(L8B):
                 p = C.c_void_p()
-                lib.check(L.cuda_malloc_host(C.byref(p), 2 * nh * CHUNK))
-                a = np.frombuffer((C.c_uint8 * (2 * nh * CHUNK)).from_address(p.value), dtype=np.uint8)
+                lib.check(L.cuda_malloc_host(C.byref(p), 2 * nhc * CHUNK))
+                a = np.frombuffer((C.c_uint8 * (2 * nhc * CHUNK)).from_address(p.value), dtype=np.uint8)
                 a[:] = (l * 11 + rank) & 0xFF
                 host_ptrs.append(p.value)
-            # destination ids are a permutation of the first nh blocks of the decode cache: one contiguous region
-            e_setup = Setup(e_args, torch, lib, device=local_rank, dst_contig_ptr=peer_cache.value, dst_blocks=nh,
-                            src_ptrs=host_ptrs)
+            if e_path == "kernel":
+                # ONE zero-copy kernel per step: SMs read host memory and store into the peer (contiguous-per-block)
+                e_args.cache_blocks = nhc
+                e_setup = Setup(e_args, torch, lib, device=local_rank, dst_contig_ptr=peer_cache.value, dst_blocks=nh,
+                                src_ptrs=[p for p in host_ptrs])
+            else:
+                assert L.copy_stream_create(C.byref(cs), L8B, nh) == 0
         else:
             lib.check(L.cuda_malloc_host(C.byref(host_out), nh * BLOCK_BYTES))
             C.memset(host_out.value, 0, nh * BLOCK_BYTES)
+
+        def prefill_step(k, value):
+            if e_path == "kernel":
+                e_setup.step(k, done_flag=peer_flag, done_value=value)
+                return
+            # legacy CopyStream: requests of 64 consecutive host blocks at random request slots -> copy engines into HBM
+            # staging, one kernel per layer storing into the peer's cache over NVLink; then the completion flag
+            slots_ = rng_e.permutation(nhc // BLOCKS_PER_REQ)[:nh // BLOCKS_PER_REQ]
+            sid = np.concatenate([np.arange(s_ * BLOCKS_PER_REQ, (s_ + 1) * BLOCKS_PER_REQ) for s_ in slots_]).astype(np.int32)
+            did = rng_e.permutation(nh).astype(np.int32)
+            lib.check(L.copy_stream_prepare_block_ids(cs, sid.ctypes.data, did.ctypes.data, nh))
+            for l in range(L8B):
+                lib.check(L.copy_stream_memcpy(cs, host_ptrs[l], peer_cache.value + l * dst_layer_bytes, 2,
+                                               CHUNK // 2, 2, nhc, nh))
+            lib.check(L.copy_stream_sync(cs))
+            lib.check(L.kvdp_xfer_signal(setup.xfer, peer_flag, value))
 
         def timed_e2e(k0, count):
             torch.cuda.synchronize()
             dist.barrier()
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            st = e_setup.stream if is_prefill else wait_stream
+            st = ((e_setup.stream if e_path == "kernel" else setup.stream) if is_prefill else wait_stream)
             a.record(st)
             for k in range(count):
                 seq["v"] += 1
                 if is_prefill:
-                    e_setup.step(k0 + k, done_flag=peer_flag, done_value=seq["v"])
+                    prefill_step(k0 + k, seq["v"])
                 else:
                     lib.check(L.kvdp_stream_wait_flag(C.c_void_p(wait_stream.cuda_stream), flag_ptr, seq["v"]))
                     lib.check(L.cuda_memcpy_async(host_out, own_cache, nh * BLOCK_BYTES,
@@ -225,7 +250,8 @@ def run_multi(args, rank, local_rank, world):
         bad = torch.zeros(1, dtype=torch.int64, device="cuda")
         if not is_prefill:      # what arrived in host memory: layer l of every block is the partner's fill byte of layer l
             got = torch.from_numpy(np.frombuffer((C.c_uint8 * (nh * BLOCK_BYTES)).from_address(host_out.value),
-                                                 dtype=np.uint8)).view(nh, L8B, 2 * CHUNK)
+                                                 dtype=np.uint8))
+            got = got.view(nh, L8B, 2 * CHUNK) if e_path == "kernel" else got.view(L8B, 1, 2 * nh * CHUNK).transpose(0, 1)
             for l in range(L8B):
                 bad += int((got[:, l] != ((l * 11 + partner) & 0xFF)).sum())
         dist.all_reduce(bad, op=dist.ReduceOp.SUM)
@@ -234,11 +260,19 @@ def run_multi(args, rank, local_rank, world):
         e2e = {"value": P * nh * BLOCK_BYTES * k_e / sec_e / GB, "unit": "GB/s",
                "h2d_bytes_per_step": P * nh * BLOCK_BYTES, "d2h_bytes_per_step": P * nh * BLOCK_BYTES, "steps": k_e,
                "verification": "all bytes of the decode-side host buffers",
-               "api": "kvdp_plan_contig over pinned host layer pointers (prefill side) -> peer-mapped decode cache, "
-                      "kvdp_xfer_run with in-kernel completion flag; decode side: kvdp_stream_wait_flag + cuda_memcpy_async "
-                      "into pinned host memory; one launch per step, PCIe-bound per prefill GPU. Every step carries the same "
+               "path": e_path,
+               "api": ("legacy CopyStream on the prefill side (copy_stream_prepare_block_ids + 32 x copy_stream_memcpy from "
+                       "pinned host layers into the PEER-mapped decode cache: copy engines host -> HBM staging, one kernel "
+                       "per layer staging -> peer over NVLink; copy_stream_sync + kvdp_xfer_signal of the completion flag)"
+                       if e_path != "kernel" else
+                       "kvdp_plan_contig over pinned host layer pointers (prefill side) -> peer-mapped decode cache, "
+                       "kvdp_xfer_run with in-kernel completion flag, one zero-copy launch per step") +
+                      "; decode side: kvdp_stream_wait_flag + cuda_memcpy_async "
+                      "into pinned host memory; PCIe-bound per prefill GPU. Every step carries the same "
                       "payload into the same cache region, so step k+1's stores overlapping step k's download are benign "
                       "here; a deployment hands out distinct blocks per request"}
+        if cs.value:
+            L.copy_stream_destroy(cs)
         for p in host_ptrs:
             L.cuda_free_host(C.c_void_p(p))
         if host_out.value:
