@@ -221,7 +221,7 @@ def run_multi(args, rank, local_rank, world):
             lib.check(L.copy_stream_sync(cs))
             lib.check(L.kvdp_xfer_signal(setup.xfer, peer_flag, value))
 
-        def timed_e2e(k0, count):
+        def timed_e2e(k0, count, download=True):
             torch.cuda.synchronize()
             dist.barrier()
             torch.cuda.synchronize()
@@ -234,8 +234,9 @@ def run_multi(args, rank, local_rank, world):
                     prefill_step(k0 + k, seq["v"])
                 else:
                     lib.check(L.kvdp_stream_wait_flag(C.c_void_p(wait_stream.cuda_stream), flag_ptr, seq["v"]))
-                    lib.check(L.cuda_memcpy_async(host_out, own_cache, nh * BLOCK_BYTES,
-                                                  C.c_void_p(wait_stream.cuda_stream)))
+                    if download:
+                        lib.check(L.cuda_memcpy_async(host_out, own_cache, nh * BLOCK_BYTES,
+                                                      C.c_void_p(wait_stream.cuda_stream)))
             b.record(st)
             torch.cuda.synchronize()
             dist.barrier()
@@ -247,6 +248,7 @@ def run_multi(args, rank, local_rank, world):
             lib.check(L.kvdp_memset(own_cache, 0, nh * BLOCK_BYTES))
         timed_e2e(0, 1)
         sec_e = timed_e2e(1, k_e)
+        sec_half = timed_e2e(1 + k_e, max(2, k_e // 4), download=False)   # the same steps without the decode-side download
         bad = torch.zeros(1, dtype=torch.int64, device="cuda")
         if not is_prefill:      # what arrived in host memory: layer l of every block is the partner's fill byte of layer l
             got = torch.from_numpy(np.frombuffer((C.c_uint8 * (nh * BLOCK_BYTES)).from_address(host_out.value),
@@ -261,6 +263,10 @@ def run_multi(args, rank, local_rank, world):
                "h2d_bytes_per_step": P * nh * BLOCK_BYTES, "d2h_bytes_per_step": P * nh * BLOCK_BYTES, "steps": k_e,
                "verification": "all bytes of the decode-side host buffers",
                "path": e_path,
+               "host_to_decode_cache_only_GBps": P * nh * BLOCK_BYTES * max(2, k_e // 4) / sec_half / GB,
+               "note": "value = full trip host -> host; host_to_decode_cache_only = the same steps stopping in the decode "
+                       "GPU's HBM (what r01 reported). With several pairs the full trip is bounded by the host: its memory "
+                       "is read by every prefill GPU and written by every decode GPU at once",
                "api": ("legacy CopyStream on the prefill side (copy_stream_prepare_block_ids + 32 x copy_stream_memcpy from "
                        "pinned host layers into the PEER-mapped decode cache: copy engines host -> HBM staging, one kernel "
                        "per layer staging -> peer over NVLink; copy_stream_sync + kvdp_xfer_signal of the completion flag)"
