@@ -402,6 +402,20 @@ def run_multi(args, rank, local_rank, world):
 
         nccl_steps()  # warm-up (NCCL connection setup)
         nccl_value = P * pairs * BLOCK_BYTES * nsteps_c / timed_default_stream(nccl_steps) / GB
+        # what NCCL delivered in its last step is byte-equal to the source relayout, hence to what the push delivers
+        # (SURVEY D.2 "NCCL path byte-equal to push path"): blocks s_ids of the prefill partner, in list order
+        bad_n = torch.zeros(1, dtype=torch.int64, device="cuda")
+        if not is_prefill:
+            sperm_p = np.random.Generator(np.random.PCG64(1234 + partner)).permutation(n).astype(np.int32)
+            o_n = ((nsteps_c - 1) % max(1, n // pairs)) * pairs
+            s_n = torch.from_numpy(sperm_p[o_n:o_n + pairs].astype(np.int64)).cuda()
+            got_n = staging.view(torch.int64).view(pairs, L8B, 2, CHUNK // 8)
+            for l in range(L8B):
+                src = synth_words(torch, layer_seed(partner, l), 2 * n * CHUNK).view(2, n, CHUNK // 8)
+                bad_n += (src[:, s_n].transpose(0, 1) != got_n[:, l]).sum()
+        dist.all_reduce(bad_n, op=dist.ReduceOp.SUM)
+        if int(bad_n.item()) != 0:
+            raise RuntimeError("NCCL comparator: %d words differ from the source relayout" % int(bad_n.item()))
         memcpy_steps()
         memcpy_value = P * pairs * BLOCK_BYTES * nsteps_c / timed_default_stream(memcpy_steps) / GB
 
@@ -444,7 +458,9 @@ def run_multi(args, rank, local_rank, world):
                          "frac_of_nominal_900": r["per_direction"] / NVLINK_PEAK_NOMINAL,
                          "note": "achieved = payload bytes per direction on the busiest port / time"},
             "comparators": {"nccl_send_recv_GBps": nccl_value, "cuda_memcpy_peer_GBps": memcpy_value,
-                            "steps": nsteps_c},
+                            "steps": nsteps_c,
+                            "nccl_payload_check": None if nccl_value is None else
+                            "all bytes of the last NCCL step equal the source relayout (and so the push path's result)"},
             "options": {k: lib.get_option(k) for k in ("copy_path", "tile_bytes", "stages", "ctas_per_sm")},
             "gpu_launches": launches, "clocks": clk, "env": env_info(torch, local_rank),
             "e2e": e2e, "token_transfer": token, "reshard": reshard,
