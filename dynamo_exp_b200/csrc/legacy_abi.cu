@@ -27,6 +27,8 @@ struct HostDma {
   bool drained_valid[2] = {false, false};
   cudaEvent_t tail = nullptr;                     // last DMA enqueued (offload: the data is on the host after it)
   bool tail_valid = false;
+  cudaEvent_t kernel_tail = nullptr;              // last zero-copy kernel of the main stream that touched host memory
+  bool host_kernel_pending = false;
   void* staging[2] = {nullptr, nullptr};
   size_t cap = 0;
   int next = 0;
@@ -149,6 +151,7 @@ void host_dma_destroy(HostDma& h) {
     h.staging[i] = nullptr;
   }
   if (h.tail) cudaEventDestroy(h.tail);
+  if (h.kernel_tail) cudaEventDestroy(h.kernel_tail);
   if (h.ids_ok) h.ids.destroy();
   if (h.dma) cudaStreamDestroy(h.dma);
   h = HostDma();
@@ -189,6 +192,7 @@ int host_dma_prepare(CopyStream* cs, bool host_is_src, size_t need_bytes) {
       KVDP_CUDA(cudaEventCreateWithFlags(&h.drained[i], cudaEventDisableTiming));
     }
     KVDP_CUDA(cudaEventCreateWithFlags(&h.tail, cudaEventDisableTiming));
+    KVDP_CUDA(cudaEventCreateWithFlags(&h.kernel_tail, cudaEventDisableTiming));
   }
   if (!h.ids_ok) {
     if (int rc = h.ids.init(std::max(cs->num_blocks, 1), cs->device)) return rc;
@@ -232,6 +236,11 @@ int host_dma_layer(CopyStream* cs, const void* src, void* dst, bool host_is_src,
   const size_t chunk = (size_t)suffix_dim * (size_t)elem_size;
   const size_t need = (size_t)prefix_dim * (size_t)n * chunk;
   if (int rc = host_dma_prepare(cs, host_is_src, need)) return rc;
+  if (h.host_kernel_pending) {  // an earlier zero-copy kernel of this handle may still be reading / writing host memory
+    KVDP_CUDA(cudaEventRecord(h.kernel_tail, cs->stream));
+    KVDP_CUDA(cudaStreamWaitEvent(h.dma, h.kernel_tail, 0));
+    h.host_kernel_pending = false;
+  }
   const int slot = h.next;
   h.next ^= 1;
   char* stage = (char*)h.staging[slot];
@@ -418,6 +427,7 @@ int copy_stream_memcpy(CopyStream* cs, const void* src_data, void* dst_data, int
   if (int rc = launch_3d(src_data, dst_data, cs->ids.d_src(), cs->ids.d_dst(), cs->num_blocks, prefix_dim,
                          suffix_dim, elem_size, src_block_dim, dst_block_dim, host, cs->stream))
     return rc;
+  if (host) cs->hd.host_kernel_pending = true;
   return cs->ids.mark_in_use(cs->stream);
 }
 
@@ -427,6 +437,7 @@ int copy_stream_sync(CopyStream* cs) {
   KVDP_CUDA(cudaStreamSynchronize(cs->stream));
   if (cs->hd.dma) KVDP_CUDA(cudaStreamSynchronize(cs->hd.dma));  // offloads finish on the DMA stream
   cs->hd.tail_valid = false;
+  cs->hd.host_kernel_pending = false;
   return 0;
 }
 

@@ -675,3 +675,40 @@ def test_copy_stream_coalesced_dma_host_path(gpu, oracle, host_path):
         assert np.array_equal(back[l].array, want_back[l]), ("offload", l)
     assert L.copy_stream_destroy(cs) == 0
     gpu.set_option("host_path", 0)
+
+
+def test_copy_stream_dma_path_is_ordered_behind_zero_copy_kernels_of_the_same_handle(gpu, oracle):
+    """Offload a few scattered blocks with the kernel path (SMs write host memory), then, with no sync in between, onboard a
+    long run that covers those host blocks with the copy-engine path: the DMA must see what the kernel wrote."""
+    L = gpu.lib()
+    layers, nh, nd, suffix, elem = 2, 32, 40, 64 * 1024, 2
+    chunk = suffix * elem
+    host = [PinnedBuf(gpu, 2 * nh * chunk) for _ in range(layers)]
+    dev_a = [DevBuf(gpu, 2 * nd * chunk) for _ in range(layers)]
+    dev_b = [DevBuf(gpu, 2 * nd * chunk) for _ in range(layers)]
+    a_np = []
+    for l, d in enumerate(dev_a):
+        a = payload(d.nbytes, 900 + l)
+        d.upload(a)
+        a_np.append(a)
+    cs = C.c_void_p()
+    assert L.copy_stream_create(C.byref(cs), layers, nh) == 0
+    for rnd in range(5):
+        s_dev = permutation(nd, 50 + rnd)[:5].copy()
+        s_host = np.array([3, 8, 13, 21, 30], dtype=np.int32)
+        assert L.copy_stream_prepare_block_ids(cs, s_dev.ctypes.data, s_host.ctypes.data, 5) == 0
+        for l in range(layers):
+            assert L.copy_stream_memcpy(cs, dev_a[l].ptr, host[l].ptr, 2, suffix, elem, nd, nh) == 0
+        run_h = np.arange(0, 32, dtype=np.int32)
+        run_d = permutation(nd, 70 + rnd)[:32].copy()
+        assert L.copy_stream_prepare_block_ids(cs, run_h.ctypes.data, run_d.ctypes.data, 32) == 0
+        for l in range(layers):
+            assert L.copy_stream_memcpy(cs, host[l].ptr, dev_b[l].ptr, 2, suffix, elem, nh, nd) == 0
+        assert L.copy_stream_sync(cs) == 0
+        for l in range(layers):
+            got = dev_b[l].download().reshape(2, nd, chunk)
+            src = a_np[l].reshape(2, nd, chunk)
+            for hb, db in zip(s_host, s_dev):
+                where = int(run_d[hb])                     # host block hb went to device block run_d[hb]
+                assert np.array_equal(got[:, where], src[:, int(db)]), (rnd, l, int(hb))
+    assert L.copy_stream_destroy(cs) == 0
