@@ -70,6 +70,26 @@ def run(h2d, d2h, ctas=0):
     print("h2d=%-6s d2h=%-6s host_ctas=%3d  total %.1f GB/s" % (h2d, d2h, ctas, best), flush=True)
 
 
+def run_chunked(chunk_mib):
+    """Both directions with plain DMAs of `chunk_mib` MiB each: what the copy engines reach at that DMA size."""
+    n = chunk_mib << 20
+    best = 0
+    for rep in range(3):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for l in range(layers):
+            for o in range(0, layer_bytes, n):
+                lib.check(L.cuda_memcpy_async(d_in[l].data_ptr() + o, h_in[l] + o, n, C.c_void_p(s1.cuda_stream)))
+                lib.check(L.cuda_memcpy_async(h_out[l] + o, d_out[l].data_ptr() + o, n, C.c_void_p(s2.cuda_stream)))
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if rep:
+            best = max(best, 2 * payload / dt / GB)
+    print("dma both ways, %3d MiB per DMA: total %.1f GB/s" % (chunk_mib, best), flush=True)
+
+
+for mib in (1, 2, 8, 32, 128):
+    run_chunked(mib)
 for combo in ((None, "kernel"), ("kernel", None), ("dma", None), (None, "dma"), ("dma", "dma"), ("kernel", "kernel"),
               ("kernel", "dma"), ("dma", "kernel")):
     run(*combo)
