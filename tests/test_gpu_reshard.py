@@ -203,3 +203,10 @@ def test_host_tier_under_a_concurrent_copy_stream(gpu, oracle):
     tier.close()
     tier_b.close()
     n_eng.close()
+
+
+@pytest.mark.parametrize("src_tp,dst_tp", [(1, 2), (2, 4), (4, 1), (2, 16), (16, 4)])
+def test_reshard_16_heads_head_size_6_as_in_the_reference_scatter_test(gpu, oracle, src_tp, dst_tp):
+    """The geometry of the reference's own scatter test (kv/layer.rs:1934-2015: 16 heads, head size 6): 12-byte head rows,
+    so runs of 12..96 bytes whose alignment is 4; non-identity ids."""
+    run_reshard(gpu, oracle, src_tp, dst_tp, L=2, H=16, D=6, bs=4, E=2, Np=6, Nd=7, sid=[4, 1, 5], did=[0, 6, 3], path=0)
