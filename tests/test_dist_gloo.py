@@ -99,3 +99,53 @@ def test_range_helpers_match_the_reference_docstrings():
     s, d = get_same_length_ranges([[0, 9]], [[0, 3], [10, 15]])
     assert s == [[0, 3], [4, 9]] and d == [[0, 3], [10, 15]]
     assert all(a[1] - a[0] == b[1] - b[0] for a, b in zip(s, d))
+
+
+def test_reshard_leg_configurations_and_canonical_data_are_deterministic():
+    """Host-side pieces of the multi-GPU reshard leg (bench_reshard.py), on the CPU: the TP configurations each GPU count
+    runs, the senders every decode rank waits for, and the closed-form canonical cache every rank regenerates."""
+    import types
+
+    import torch
+
+    import bench_reshard as br
+    from dynamo_exp_b200.connector import tp_targets
+    assert br.configs_for(8) == [(4, 2), (4, 4)] and br.configs_for(4) == [(2, 2), (2, 1)] and br.configs_for(2) == [(1, 1)]
+    for n, cfgs in ((2, br.configs_for(2)), (4, br.configs_for(4)), (8, br.configs_for(8))):
+        for p_tp, d_tp in cfgs:
+            assert p_tp + d_tp <= n
+            cover = {}
+            for p in range(p_tp):
+                for q in tp_targets(p_tp, d_tp, p):
+                    cover.setdefault(q, []).append(p)
+            assert sorted(cover) == list(range(d_tp))                       # every decode rank hears from someone
+            assert all(len(v) == max(1, p_tp // d_tp) for v in cover.values())
+    cpu = types.SimpleNamespace(arange=lambda n, dtype, device: torch.arange(n, dtype=dtype), int64=torch.int64,
+                                int16=torch.int16)
+    saved = (br.BS, br.D70)
+    try:
+        br.BS, br.D70 = 4, 8                                                # small geometry, same arithmetic
+        a, b, c = br.canonical_layer(cpu, 3, 5), br.canonical_layer(cpu, 3, 5), br.canonical_layer(cpu, 4, 5)
+    finally:
+        br.BS, br.D70 = saved
+    assert a.shape == (2, 5, 4, 8, 8) and torch.equal(a, b) and not torch.equal(a, c)
+    assert len(set(a.flatten().tolist())) > a.numel() // 2                  # values vary: a misrouted chunk cannot pass
+
+
+def test_reference_connector_range_helpers_agree_with_the_restatement():
+    """oracle/ref_triton.py replays the reference's range splitting around its Triton kernel; its helpers must agree with
+    the product's get_ranges / get_same_length_ranges on the reference's docstring examples and on random id lists."""
+    import numpy as np
+
+    from dynamo_exp_b200.connector import get_ranges, get_same_length_ranges
+    from oracle import ref_triton
+    assert ref_triton._ranges([0, 1, 2, 4, 5, 6]) == get_ranges([0, 1, 2, 4, 5, 6]) == [[0, 2], [4, 6]]
+    s, d = [[0, 2], [4, 8]], [[1, 3], [5, 7], [9, 10]]
+    assert ref_triton._same_length(s, d) == tuple(get_same_length_ranges(s, d))
+    rng = np.random.default_rng(3)
+    for _ in range(50):
+        n = int(rng.integers(1, 20))
+        a = sorted(int(x) for x in rng.choice(60, size=n, replace=False))
+        b = sorted(int(x) for x in rng.choice(60, size=n, replace=False))
+        assert ref_triton._same_length(ref_triton._ranges(a), ref_triton._ranges(b)) == \
+            tuple(get_same_length_ranges(get_ranges(a), get_ranges(b)))
