@@ -416,7 +416,9 @@ int copy_stream_memcpy(CopyStream* cs, const void* src_data, void* dst_data, int
     return dma_loop_3d(src_data, dst_data, cs->h_src.data(), cs->h_dst.data(), cs->num_blocks, prefix_dim,
                        suffix_dim, elem_size, src_block_dim, dst_block_dim, cs->stream);
   // exactly one side in pinned host memory and long consecutive runs on that side: copy engines + one kernel
+  // (the two staging slots hold one layer's worth of the id set each: not for id sets beyond 1 GiB per layer)
   if ((sk == kPinned) != (dk == kPinned) && options().host_path == 0 &&
+      (size_t)prefix_dim * (size_t)cs->num_blocks * (size_t)suffix_dim * (size_t)elem_size <= ((size_t)1 << 30) &&
       host_dma_plan(cs, sk == kPinned, (size_t)suffix_dim * (size_t)elem_size))
     return host_dma_layer(cs, src_data, dst_data, sk == kPinned, prefix_dim, suffix_dim, elem_size, src_block_dim,
                           dst_block_dim);
