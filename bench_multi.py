@@ -221,7 +221,7 @@ def run_multi(args, rank, local_rank, world):
             lib.check(L.copy_stream_sync(cs))
             lib.check(L.kvdp_xfer_signal(setup.xfer, peer_flag, value))
 
-        def timed_e2e(k0, count, download=True):
+        def timed_e2e(k0, count, download="full"):
             torch.cuda.synchronize()
             dist.barrier()
             torch.cuda.synchronize()
@@ -234,9 +234,10 @@ def run_multi(args, rank, local_rank, world):
                     prefill_step(k0 + k, seq["v"])
                 else:
                     lib.check(L.kvdp_stream_wait_flag(C.c_void_p(wait_stream.cuda_stream), flag_ptr, seq["v"]))
-                    if download:
-                        lib.check(L.cuda_memcpy_async(host_out, own_cache, nh * BLOCK_BYTES,
-                                                      C.c_void_p(wait_stream.cuda_stream)))
+                    # "full": the step's blocks go on to this side's pinned host memory; "probe": 8 bytes of the step's
+                    # result are read back (the onboard leg's device -> host read)
+                    lib.check(L.cuda_memcpy_async(host_out, own_cache, nh * BLOCK_BYTES if download == "full" else 8,
+                                                  C.c_void_p(wait_stream.cuda_stream)))
             b.record(st)
             torch.cuda.synchronize()
             dist.barrier()
@@ -247,36 +248,46 @@ def run_multi(args, rank, local_rank, world):
         if not is_prefill:
             lib.check(L.kvdp_memset(own_cache, 0, nh * BLOCK_BYTES))
         timed_e2e(0, 1)
-        sec_e = timed_e2e(1, k_e)
-        sec_half = timed_e2e(1 + k_e, max(2, k_e // 4), download=False)   # the same steps without the decode-side download
+        sec_full = timed_e2e(1, k_e)
         bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+
+        def check_bytes(flat):
+            got = flat.view(nh, L8B, 2 * CHUNK) if e_path == "kernel" else flat.view(L8B, 1, 2 * nh * CHUNK).transpose(0, 1)
+            return sum(int((got[:, l] != ((l * 11 + partner) & 0xFF)).sum()) for l in range(L8B))
         if not is_prefill:      # what arrived in host memory: layer l of every block is the partner's fill byte of layer l
-            got = torch.from_numpy(np.frombuffer((C.c_uint8 * (nh * BLOCK_BYTES)).from_address(host_out.value),
-                                                 dtype=np.uint8))
-            got = got.view(nh, L8B, 2 * CHUNK) if e_path == "kernel" else got.view(L8B, 1, 2 * nh * CHUNK).transpose(0, 1)
-            for l in range(L8B):
-                bad += int((got[:, l] != ((l * 11 + partner) & 0xFF)).sum())
+            bad += check_bytes(torch.from_numpy(np.frombuffer((C.c_uint8 * (nh * BLOCK_BYTES)).from_address(host_out.value),
+                                                              dtype=np.uint8)))
+            lib.check(L.kvdp_memset(own_cache, 0, nh * BLOCK_BYTES))
+        sec_on = timed_e2e(1 + k_e, k_e, download="probe")
+        if not is_prefill:      # ... and what the onboard leg left in the decode GPU's cache
+            bad += check_bytes(torch.as_tensor(CudaArray(own_cache.value, nh * BLOCK_BYTES), device="cuda"))
         dist.all_reduce(bad, op=dist.ReduceOp.SUM)
         if int(bad.item()) != 0:
-            raise RuntimeError("e2e: %d bytes in decode-side host memory differ from the prefill-side host source" % int(bad.item()))
-        e2e = {"value": P * nh * BLOCK_BYTES * k_e / sec_e / GB, "unit": "GB/s",
-               "h2d_bytes_per_step": P * nh * BLOCK_BYTES, "d2h_bytes_per_step": P * nh * BLOCK_BYTES, "steps": k_e,
-               "verification": "all bytes of the decode-side host buffers",
-               "path": e_path,
-               "host_to_decode_cache_only_GBps": P * nh * BLOCK_BYTES * max(2, k_e // 4) / sec_half / GB,
-               "note": "value = full trip host -> host; host_to_decode_cache_only = the same steps stopping in the decode "
-                       "GPU's HBM (what r01 reported). With several pairs the full trip is bounded by the host: its memory "
-                       "is read by every prefill GPU and written by every decode GPU at once",
-               "api": ("legacy CopyStream on the prefill side (copy_stream_prepare_block_ids + 32 x copy_stream_memcpy from "
+            raise RuntimeError("e2e: %d bytes on the decode side differ from the prefill-side host source" % int(bad.item()))
+        prefill_api = ("legacy CopyStream on the prefill side (copy_stream_prepare_block_ids + 32 x copy_stream_memcpy from "
                        "pinned host layers into the PEER-mapped decode cache: copy engines host -> HBM staging, one kernel "
                        "per layer staging -> peer over NVLink; copy_stream_sync + kvdp_xfer_signal of the completion flag)"
                        if e_path != "kernel" else
                        "kvdp_plan_contig over pinned host layer pointers (prefill side) -> peer-mapped decode cache, "
-                       "kvdp_xfer_run with in-kernel completion flag, one zero-copy launch per step") +
-                      "; decode side: kvdp_stream_wait_flag + cuda_memcpy_async "
-                      "into pinned host memory; PCIe-bound per prefill GPU. Every step carries the same "
-                      "payload into the same cache region, so step k+1's stores overlapping step k's download are benign "
-                      "here; a deployment hands out distinct blocks per request"}
+                       "kvdp_xfer_run with in-kernel completion flag, one zero-copy launch per step")
+        e2e = {"value": P * nh * BLOCK_BYTES * k_e / sec_on / GB, "unit": "GB/s",
+               "leg": "onboard: blocks held in the prefill side's pinned host memory are delivered into the decode GPU's "
+                      "cache (PCIe on the prefill GPU, NVLink to the decode GPU); the decode side waits on the step's "
+                      "completion flag and reads 8 bytes of the result back to its host",
+               "h2d_bytes_per_step": P * nh * BLOCK_BYTES, "d2h_bytes_per_step": 8 * D, "steps": k_e,
+               "verification": "all bytes of the step's region of every decode cache, and of the decode-side host "
+                               "buffers in the full trip",
+               "path": e_path,
+               "full_trip_host_to_host": {
+                   "value": P * nh * BLOCK_BYTES * k_e / sec_full / GB, "unit": "GB/s", "steps": k_e,
+                   "h2d_bytes_per_step": P * nh * BLOCK_BYTES, "d2h_bytes_per_step": P * nh * BLOCK_BYTES,
+                   "note": "the same steps with the decode side copying every step's blocks on to ITS pinned host memory "
+                           "(kvdp_stream_wait_flag + cuda_memcpy_async), pipelined with the next step. No deployment "
+                           "moves KV host -> GPU -> NVLink -> GPU -> host; with several pairs it is bounded by the host, "
+                           "whose memory is read by every prefill GPU and written by every decode GPU at once. Every "
+                           "step carries the same payload into the same cache region, so step k+1's stores overlapping "
+                           "step k's download are benign here"},
+               "api": prefill_api + "; decode side: kvdp_stream_wait_flag; PCIe-bound per prefill GPU"}
         if cs.value:
             L.copy_stream_destroy(cs)
         for p in host_ptrs:
