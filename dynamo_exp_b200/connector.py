@@ -514,12 +514,21 @@ class DynamoKvdpConnector:
         `slot_mapping` with a head slice, a send, and `reshape_and_cache_flash` on the other side). Asynchronous,
         completion and notification as for write_blocks."""
         rem = self._remote(dst_engine_id)
-        if self._is_mla:
-            raise KvError("token-granular transfer of the MLA latent cache is not implemented")
         local_slots, remote_slots = list(local_slots), list(remote_slots)
         if len(local_slots) != len(remote_slots):
             raise KvError("local and remote slot lists must have the same length")
-        if local_slots:
+        if local_slots and self._is_mla:
+            # latent cache: whole token rows, no head split, the same rows to every target rank (the reference's
+            # deepseek branch: `keys.append(key_cache[current_slot_mapping])` / `kv_cache[slot_mapping] = copy_from`,
+            # patch:1662-1665, 1748-1752)
+            if getattr(rem, "_mla_push_tokens", None) is None:
+                row = self.block_len // self.block_size
+                rem._mla_push_tokens = [CopyPlan.block_copy_raw(
+                    self._layer_ptrs, rem.layer_ptrs[q], 1, self.num_blocks * self.block_size,
+                    rem.num_blocks * self.block_size, row, 1, self.device) for q in rem.targets]
+            for plan in rem._mla_push_tokens:
+                self._engine.run(plan, local_slots, remote_slots, num_layers=self.num_layers)
+        elif local_slots:
             if getattr(rem, "push_tokens", None) is None:
                 # the block reshard plan with one-token "blocks": rows = 1, runs of one (sub-)row
                 rem.push_tokens = CopyPlan.reshard(
@@ -697,7 +706,7 @@ class DynamoKvdpConnector:
                 rem.push.close()
             for p in rem.pull:
                 p.close()
-            for p in getattr(rem, "_mla_push", []):
+            for p in getattr(rem, "_mla_push", []) + (getattr(rem, "_mla_push_tokens", None) or []):
                 p.close()
             for ptr in rem.mapped:
                 L.kvdp_ipc_close(C.c_void_p(ptr))

@@ -165,6 +165,18 @@ def test_mla_latent_cache_is_replicated(gpu):
             got = dbufs[r][l].download().reshape(nb, bs, hd)
             assert np.array_equal(got[[0, 3]], src_h[l][[5, 1]])
         assert decs[r].get_new_notifs() == {"p:0": ["mla"]}
+    # token-granular form on the latent cache (the NCCL connector's deepseek branch, patch:1662-1665, 1748-1752): whole
+    # token rows, replicated to every target rank; untouched slots keep their content
+    before = [[b.download().reshape(nb * bs, hd) for b in dbufs[r]] for r in range(2)]
+    s_slots, d_slots = [21, 3, 8, 14], [1, 22, 9, 17]
+    pre.write_token_rows(s_slots, d_slots, "d", "mla-tok")
+    pre.sync()
+    for r in range(2):
+        for l in range(L):
+            want = before[r][l].copy()
+            want[d_slots] = src_h[l].reshape(nb * bs, hd)[s_slots]
+            assert np.array_equal(dbufs[r][l].download().reshape(nb * bs, hd), want), (r, l)
+        assert decs[r].get_new_notifs() == {"p:0": ["mla-tok"]}
     for c in [pre] + decs:
         c.shutdown()
 
