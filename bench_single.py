@@ -217,12 +217,13 @@ def e2e_legacy(torch, lib, args, steps, warmup):
             lib.check(L.copy_stream_sync(cs_off))
         return time.perf_counter() - t0, ids
 
-    t_total, timed, ids = 0.0, 0, None
+    t_total, timed, ids, step_ms = 0.0, 0, None, []
     for k in range(steps + warmup):
         dt, ids = one_step()
         if k >= warmup:
             t_total += dt
             timed += 1
+            step_ms.append(round(dt * 1e3, 3))
     # every byte of the last step, both directions
     for l in range(L8B):
         want = torch.from_numpy(host_in[l]).view(2, nh, CHUNK)[:, torch.from_numpy(ids[0].astype(np.int64))].cuda()
@@ -274,7 +275,7 @@ def e2e_legacy(torch, lib, args, steps, warmup):
     sec = t_total / timed
     payload = pairs * BLOCK_BYTES
     return {"value": 2 * payload / sec / GB, "unit": "GB/s", "h2d_bytes_per_step": payload, "d2h_bytes_per_step": payload,
-            "ms_per_step": sec * 1e3, "steps": timed,
+            "ms_per_step": sec * 1e3, "steps": timed, "step_ms": step_ms,
             "step": "onboard %d blocks (pinned host -> HBM) + offload %d blocks (HBM -> pinned host), concurrently, "
                     "each through its own legacy CopyStream" % (pairs, pairs),
             "duplex_link_ceiling_GBps": ceil_both, "frac_of_duplex_link_ceiling": 2 * payload / sec / GB / ceil_both,
@@ -283,7 +284,8 @@ def e2e_legacy(torch, lib, args, steps, warmup):
             "offload": {"GBps": payload / t_off / GB, "d2h_link_ceiling_GBps": ceil_d2h,
                         "frac_of_link_ceiling": payload / t_off / GB / ceil_d2h},
             "h2d_link_ceiling_GBps": ceil_h2d, "frac_of_link_ceiling": payload / t_on / GB / ceil_h2d,
-            "host_path": {0: "auto: one DMA per run of consecutive host blocks through HBM staging + one kernel per layer "
+            "host_dma_piece_kib": lib.get_option("host_dma_piece_kib"),
+            "host_path": {0: "auto: DMAs over each run of consecutive host blocks (pieces of one size) through HBM staging + one kernel per layer "
                              "when the host-side runs average >= 1 MiB, else SMs read / write pinned memory",
                           1: "per-chunk cudaMemcpyAsync loop", 2: "TMA kernel on pinned memory",
                           3: "SMs read / write pinned memory"}[lib.get_option("host_path")],

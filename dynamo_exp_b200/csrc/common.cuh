@@ -32,6 +32,7 @@ struct Options {
   int64_t host_path = 0;    // pinned host memory: 0 auto (CopyStream: coalesced DMA when the host-side ids form long
                             // runs, else the vector kernel), 1 per-chunk DMA loop, 2 TMA kernel, 3 vector kernel
   int64_t host_ctas = 0;    // CTAs used when one side is host memory (0 = default)
+  int64_t host_dma_piece_kib = 8192;  // coalesced DMA path: runs are issued in pieces of at most this size (0 = whole runs)
   int64_t l2_hint = 0;      // path 3: 1 = evict_first on loads, 2 = on stores, 3 = both
   int64_t vec32 = 0;        // path 1: 1 = 256-bit loads/stores when everything is 32-byte aligned
   int64_t hash_stages = 0;  // chained hashing of a big batch: request ranges whose chains overlap the next range's

@@ -41,7 +41,11 @@ struct kvdp_host_tier {
 namespace {
 
 int dma_ranges(kvdp_host_tier* t, const int32_t* host_ids, int n, char* slot, bool to_host) {
-  // one DMA per maximal run of consecutive host ids (slot positions are consecutive by construction)
+  // one DMA per maximal run of consecutive host ids (slot positions are consecutive by construction), issued in pieces of
+  // one size: an offload and an onboard running at once share the link evenly only when their DMAs are equally large
+  // (see host_dma_layer in legacy_abi.cu)
+  const size_t piece_opt = (size_t)options().host_dma_piece_kib << 10;
+  const size_t piece = piece_opt ? piece_opt : ~(size_t)0;
   int i = 0;
   while (i < n) {
     int j = i + 1;
@@ -49,10 +53,13 @@ int dma_ranges(kvdp_host_tier* t, const int32_t* host_ids, int n, char* slot, bo
     char* h = t->pinned + (int64_t)host_ids[i] * t->block_bytes;
     char* s = slot + (int64_t)i * t->block_bytes;
     const size_t bytes = (size_t)(j - i) * (size_t)t->block_bytes;
-    if (to_host)
-      KVDP_CUDA(cudaMemcpyAsync(h, s, bytes, cudaMemcpyDeviceToHost, t->copy_stream));
-    else
-      KVDP_CUDA(cudaMemcpyAsync(s, h, bytes, cudaMemcpyHostToDevice, t->copy_stream));
+    for (size_t o = 0; o < bytes; o += piece) {
+      const size_t len = std::min(piece, bytes - o);
+      if (to_host)
+        KVDP_CUDA(cudaMemcpyAsync(h + o, s + o, len, cudaMemcpyDeviceToHost, t->copy_stream));
+      else
+        KVDP_CUDA(cudaMemcpyAsync(s + o, h + o, len, cudaMemcpyHostToDevice, t->copy_stream));
+    }
     i = j;
   }
   return 0;

@@ -109,6 +109,9 @@ int kvdp_set_option(const char* name, int64_t value) {
   } else if (!strcmp(name, "host_ctas")) {
     if (value < 0 || value > 4096) return fail(KVDP_EINVAL, "host_ctas out of range");
     o.host_ctas = value;
+  } else if (!strcmp(name, "host_dma_piece_kib")) {
+    if (value < 0 || value > (1 << 20)) return fail(KVDP_EINVAL, "host_dma_piece_kib must be 0..1048576");
+    o.host_dma_piece_kib = value;
   } else {
     return fail(KVDP_EINVAL, "unknown option '%s'", name);
   }
@@ -124,6 +127,7 @@ int64_t kvdp_get_option(const char* name) {
   if (!strcmp(name, "ctas_per_sm")) return o.ctas_per_sm;
   if (!strcmp(name, "host_path")) return o.host_path;
   if (!strcmp(name, "host_ctas")) return o.host_ctas;
+  if (!strcmp(name, "host_dma_piece_kib")) return o.host_dma_piece_kib;
   if (!strcmp(name, "l2_hint")) return o.l2_hint;
   if (!strcmp(name, "vec32")) return o.vec32;
   if (!strcmp(name, "hash_stages")) return o.hash_stages;

@@ -46,7 +46,9 @@ int kvdp_version(void);
  * "tile_bytes", "stages", "ctas_per_sm", "host_path" (pinned memory: 0 auto = a CopyStream whose
  * host-side ids form runs of >= 1 MiB on average moves them with one DMA per run through an HBM staging buffer plus one
  * kernel, anything else uses the vector kernel; 1 per-chunk DMA loop as the reference does; 2 TMA kernel; 3 vector
- * kernel always), "host_ctas", "l2_hint",
+ * kernel always), "host_ctas", "host_dma_piece_kib" (the copy-engine path of a CopyStream and the host tier issue each
+ * host-side run in pieces of this many KiB, default 8192, 0 = whole runs: an onboard and an offload running at once
+ * share the link evenly only when their DMAs are equally large), "l2_hint",
  * "vec32" (copy path 1: 256-bit loads/stores when every pointer and stride is 32-byte aligned; +5 % on that path in HBM,
  * no change over NVLink), "hash_stages" (chained hashing of a big batch: number of request ranges whose chain kernels
  * run under the next range's block hashing; 0 or 1 = off, the default: everything stays on the caller's stream —

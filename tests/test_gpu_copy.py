@@ -712,3 +712,50 @@ def test_copy_stream_dma_path_is_ordered_behind_zero_copy_kernels_of_the_same_ha
                 where = int(run_d[hb])                     # host block hb went to device block run_d[hb]
                 assert np.array_equal(got[:, where], src[:, int(db)]), (rnd, l, int(hb))
     assert L.copy_stream_destroy(cs) == 0
+
+
+@pytest.mark.parametrize("piece_kib", [0, 64, 384, 8192])
+def test_copy_stream_dma_runs_in_pieces(gpu, oracle, piece_kib):
+    """host_dma_piece_kib: the copy-engine path issues each host-side run in pieces of one size. Runs of 16 and 11 chunks
+    of 128 KiB against pieces of: whole runs, less than a chunk (one chunk per DMA), 3 chunks (ragged tails), larger
+    than any run. Same bytes as the oracle in both directions."""
+    L = gpu.lib()
+    gpu.set_option("host_path", 0)
+    gpu.set_option("host_dma_piece_kib", piece_kib)
+    try:
+        layers, nh, nd, suffix, elem = 2, 64, 40, 64 * 1024, 2
+        chunk = suffix * elem
+        rng = np.random.Generator(np.random.PCG64(piece_kib + 3))
+        host = [PinnedBuf(gpu, 2 * nh * chunk) for _ in range(layers)]
+        back = [PinnedBuf(gpu, 2 * nh * chunk) for _ in range(layers)]
+        dev = [DevBuf(gpu, 2 * nd * chunk) for _ in range(layers)]
+        src_np = []
+        for l, h in enumerate(host):
+            h.array[:] = payload(h.nbytes, 700 + l)
+            src_np.append(h.array.copy())
+        pairs = 27
+        sh = rng.permutation(pairs)
+        h_ids = np.concatenate([np.arange(5, 21), np.arange(30, 41)]).astype(np.int32)[sh].copy()
+        d_ids = rng.permutation(nd)[:pairs].astype(np.int32)
+        cs = C.c_void_p()
+        assert L.copy_stream_create(C.byref(cs), layers, pairs) == 0
+        assert L.copy_stream_prepare_block_ids(cs, h_ids.ctypes.data, d_ids.ctypes.data, pairs) == 0
+        for l in range(layers):
+            assert L.copy_stream_memcpy(cs, host[l].ptr, dev[l].ptr, 2, suffix, elem, nh, nd) == 0, gpu.last_error()
+        assert L.copy_stream_sync(cs) == 0
+        want_dev = [np.zeros(2 * nd * chunk, dtype=np.uint8) for _ in range(layers)]
+        oracle.copy_blocks_layers(src_np, want_dev, h_ids, d_ids, 2, nh, nd, suffix, elem)
+        for l in range(layers):
+            assert np.array_equal(dev[l].download(), want_dev[l]), ("onboard", piece_kib, l)
+        h2 = np.concatenate([np.arange(0, 11), np.arange(48, 64)]).astype(np.int32)[rng.permutation(pairs)].copy()
+        assert L.copy_stream_prepare_block_ids(cs, d_ids.ctypes.data, h2.ctypes.data, pairs) == 0
+        for l in range(layers):
+            assert L.copy_stream_memcpy(cs, dev[l].ptr, back[l].ptr, 2, suffix, elem, nd, nh) == 0, gpu.last_error()
+        assert L.copy_stream_sync(cs) == 0
+        want_back = [np.zeros(2 * nh * chunk, dtype=np.uint8) for _ in range(layers)]
+        oracle.copy_blocks_layers(want_dev, want_back, d_ids, h2, 2, nd, nh, suffix, elem)
+        for l in range(layers):
+            assert np.array_equal(back[l].array, want_back[l]), ("offload", piece_kib, l)
+        assert L.copy_stream_destroy(cs) == 0
+    finally:
+        gpu.set_option("host_dma_piece_kib", 8192)
