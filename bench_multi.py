@@ -186,14 +186,40 @@ def run_multi(args, rank, local_rank, world):
         nhc = 2 * nh                                  # host cache: twice the step's blocks
         dst_layer_bytes = 2 * nh * CHUNK              # the first 1 GiB of the decode cache, viewed as 32 layer slabs
         cs = C.c_void_p()
-        rng_e = np.random.Generator(np.random.PCG64(4321 + rank))
+        # --e2e-links both (default): the prefill side's host blocks live in memory BOTH workers of the pair map and pin
+        # (shared_host.SharedHostRegion); the prefill GPU relays its share of a step's requests over NVLink and the decode
+        # GPU fetches the rest over its OWN PCIe link - two links instead of one for the same onboard.
+        links = 2 if (getattr(args, "e2e_links", "both") == "both" and e_path == "dma") else 1
+        from dynamo_exp_b200.shared_host import SharedHostRegion, split_for_links
+        n_req_e = nh // BLOCKS_PER_REQ
+        share = split_for_links(n_req_e, links)       # [(first, last request) per link]; link 0 = the prefill GPU
+        host_layer_bytes = 2 * nhc * CHUNK
+        region, handles_e = None, [None] * world
+        if links == 2:
+            if is_prefill:
+                region = SharedHostRegion.create(L8B * host_layer_bytes)
+            dist.all_gather_object(handles_e, region.handle() if is_prefill else None)
+            if not is_prefill:
+                region = SharedHostRegion.open(handles_e[partner])
+            dist.barrier()
+
+        def step_ids(pair_seed, k):
+            """The step's (host ids, decode-cache ids), the same on both workers of a pair."""
+            r = np.random.Generator(np.random.PCG64([4321, pair_seed, k]))
+            slots_ = r.permutation(nhc // BLOCKS_PER_REQ)[:n_req_e]
+            sid = np.concatenate([np.arange(s_ * BLOCKS_PER_REQ, (s_ + 1) * BLOCKS_PER_REQ) for s_ in slots_]).astype(np.int32)
+            return sid, r.permutation(nh).astype(np.int32)
         if is_prefill:
             for l in range(L8B):
-                p = C.c_void_p()
-                lib.check(L.cuda_malloc_host(C.byref(p), 2 * nhc * CHUNK))
-                a = np.frombuffer((C.c_uint8 * (2 * nhc * CHUNK)).from_address(p.value), dtype=np.uint8)
+                if region is not None:
+                    ptr_l = region.ptr + l * host_layer_bytes
+                else:
+                    p = C.c_void_p()
+                    lib.check(L.cuda_malloc_host(C.byref(p), host_layer_bytes))
+                    ptr_l = p.value
+                a = np.frombuffer((C.c_uint8 * host_layer_bytes).from_address(ptr_l), dtype=np.uint8)
                 a[:] = (l * 11 + rank) & 0xFF
-                host_ptrs.append(p.value)
+                host_ptrs.append(ptr_l)
             if e_path == "kernel":
                 # ONE zero-copy kernel per step: SMs read host memory and store into the peer (contiguous-per-block)
                 e_args.cache_blocks = nhc
@@ -204,20 +230,29 @@ def run_multi(args, rank, local_rank, world):
         else:
             lib.check(L.cuda_malloc_host(C.byref(host_out), nh * BLOCK_BYTES))
             C.memset(host_out.value, 0, nh * BLOCK_BYTES)
+            if links == 2:
+                host_ptrs = [region.ptr + l * host_layer_bytes for l in range(L8B)]
+                assert L.copy_stream_create(C.byref(cs), L8B, nh) == 0
+        my_share = share[0] if is_prefill else share[links - 1]
+        b0, b1 = my_share[0] * BLOCKS_PER_REQ, my_share[1] * BLOCKS_PER_REQ
+
+        def link_step(k, cache_base):
+            """This worker's share of step k through the legacy CopyStream: requests of 64 consecutive host blocks at random
+            request slots -> copy engines into HBM staging, one kernel per layer storing into the decode cache (the peer
+            mapping over NVLink on the prefill side, local memory on the decode side)."""
+            sid, did = step_ids(min(rank, partner), k)
+            sid, did = sid[b0:b1].copy(), did[b0:b1].copy()
+            if b1 > b0:
+                lib.check(L.copy_stream_prepare_block_ids(cs, sid.ctypes.data, did.ctypes.data, b1 - b0))
+                for l in range(L8B):
+                    lib.check(L.copy_stream_memcpy(cs, host_ptrs[l], cache_base + l * dst_layer_bytes, 2, CHUNK // 2, 2,
+                                                   nhc, nh))
 
         def prefill_step(k, value):
             if e_path == "kernel":
                 e_setup.step(k, done_flag=peer_flag, done_value=value)
                 return
-            # legacy CopyStream: requests of 64 consecutive host blocks at random request slots -> copy engines into HBM
-            # staging, one kernel per layer storing into the peer's cache over NVLink; then the completion flag
-            slots_ = rng_e.permutation(nhc // BLOCKS_PER_REQ)[:nh // BLOCKS_PER_REQ]
-            sid = np.concatenate([np.arange(s_ * BLOCKS_PER_REQ, (s_ + 1) * BLOCKS_PER_REQ) for s_ in slots_]).astype(np.int32)
-            did = rng_e.permutation(nh).astype(np.int32)
-            lib.check(L.copy_stream_prepare_block_ids(cs, sid.ctypes.data, did.ctypes.data, nh))
-            for l in range(L8B):
-                lib.check(L.copy_stream_memcpy(cs, host_ptrs[l], peer_cache.value + l * dst_layer_bytes, 2,
-                                               CHUNK // 2, 2, nhc, nh))
+            link_step(k, peer_cache.value)
             lib.check(L.copy_stream_sync(cs))
             lib.check(L.kvdp_xfer_signal(setup.xfer, peer_flag, value))
 
@@ -233,6 +268,9 @@ def run_multi(args, rank, local_rank, world):
                 if is_prefill:
                     prefill_step(k0 + k, seq["v"])
                 else:
+                    if links == 2:                      # this GPU's own link carries its share of the step
+                        link_step(k0 + k, own_cache.value)
+                        lib.check(L.copy_stream_sync(cs))
                     lib.check(L.kvdp_stream_wait_flag(C.c_void_p(wait_stream.cuda_stream), flag_ptr, seq["v"]))
                     # "full": the step's blocks go on to this side's pinned host memory; "probe": 8 bytes of the step's
                     # result are read back (the onboard leg's device -> host read)
@@ -270,10 +308,18 @@ def run_multi(args, rank, local_rank, world):
                        if e_path != "kernel" else
                        "kvdp_plan_contig over pinned host layer pointers (prefill side) -> peer-mapped decode cache, "
                        "kvdp_xfer_run with in-kernel completion flag, one zero-copy launch per step")
+        if links == 2:
+            prefill_api += ("; links=both: the host blocks sit in memory both workers of the pair map and pin "
+                            "(SharedHostRegion: memfd + kvdp_host_register), the prefill GPU carries requests %s of each step "
+                            "and the decode GPU fetches requests %s through its own CopyStream over its own PCIe link"
+                            % (list(range(*share[0])), list(range(*share[1]))))
         e2e = {"value": P * nh * BLOCK_BYTES * k_e / sec_on / GB, "unit": "GB/s",
                "leg": "onboard: blocks held in the prefill side's pinned host memory are delivered into the decode GPU's "
-                      "cache (PCIe on the prefill GPU, NVLink to the decode GPU); the decode side waits on the step's "
-                      "completion flag and reads 8 bytes of the result back to its host",
+                      "cache (PCIe on the prefill GPU, NVLink to the decode GPU%s); the decode side waits on the step's "
+                      "completion flag and reads 8 bytes of the result back to its host"
+                      % ("; with links=both the decode GPU fetches half of each step's requests itself over its own "
+                         "PCIe link" if links == 2 else ""),
+               "links": "both" if links == 2 else "prefill",
                "h2d_bytes_per_step": P * nh * BLOCK_BYTES, "d2h_bytes_per_step": 8 * D, "steps": k_e,
                "verification": "all bytes of the step's region of every decode cache, and of the decode-side host "
                                "buffers in the full trip",
@@ -287,11 +333,15 @@ def run_multi(args, rank, local_rank, world):
                            "whose memory is read by every prefill GPU and written by every decode GPU at once. Every "
                            "step carries the same payload into the same cache region, so step k+1's stores overlapping "
                            "step k's download are benign here"},
-               "api": prefill_api + "; decode side: kvdp_stream_wait_flag; PCIe-bound per prefill GPU"}
+               "api": prefill_api + "; decode side: kvdp_stream_wait_flag; PCIe-bound per GPU whose link is used"}
         if cs.value:
             L.copy_stream_destroy(cs)
-        for p in host_ptrs:
-            L.cuda_free_host(C.c_void_p(p))
+        if region is not None:
+            dist.barrier()
+            region.close()
+        else:
+            for p in host_ptrs:
+                L.cuda_free_host(C.c_void_p(p))
         if host_out.value:
             L.cuda_free_host(host_out)
 

@@ -102,6 +102,8 @@ PROTOTYPES = {
     "kvdp_stream_synchronize": (_i, [_vp]),
     "kvdp_stream_wait_flag": (_i, [_vp, _vp, _u32]),
     "kvdp_flag_cas64": (_i, [_vp, _u64, _u64, C.POINTER(_u64), _i32]),
+    "kvdp_host_register": (_i, [_vp, _sz]),
+    "kvdp_host_unregister": (_i, [_vp]),
     "kvdp_peer_enable": (_i, [_i32, _i32]),
     "kvdp_ipc_export": (_i, [_vp, _vp]),
     "kvdp_ipc_export_range": (_i, [_vp, _vp, C.POINTER(_u64)]),

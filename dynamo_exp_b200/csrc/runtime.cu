@@ -253,6 +253,26 @@ int kvdp_flag_cas64(uint64_t* addr, uint64_t expected, uint64_t desired, uint64_
   return 0;
 }
 
+int kvdp_host_register(void* ptr, size_t bytes) {
+  if (!ptr || bytes == 0) return fail(KVDP_EINVAL, "kvdp_host_register: NULL pointer or zero size");
+  cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail((int)e, "kvdp_host_register(%p, %zu): %s", ptr, bytes, cudaGetErrorString(e));
+  }
+  return 0;
+}
+
+int kvdp_host_unregister(void* ptr) {
+  if (!ptr) return fail(KVDP_EINVAL, "kvdp_host_unregister: NULL pointer");
+  cudaError_t e = cudaHostUnregister(ptr);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail((int)e, "kvdp_host_unregister(%p): %s", ptr, cudaGetErrorString(e));
+  }
+  return 0;
+}
+
 int kvdp_stream_synchronize(kvdp_stream_t stream) {
   KVDP_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
   return 0;

@@ -216,6 +216,17 @@ int kvdp_stream_wait_flag(kvdp_stream_t stream, uint32_t* flag, uint32_t value);
  * returns {agent_name: [...]}). */
 int kvdp_flag_cas64(uint64_t* addr, uint64_t expected, uint64_t desired, uint64_t* old, int32_t device);
 
+/* Page-lock and map a host range the caller owns (page-aligned, e.g. an mmap of a memfd or of POSIX shared memory) so
+ * that every entry point treats it like cuda_malloc_host memory (copy engines and SMs reach it; a CopyStream takes its
+ * copy-engine path on it). A host tier kept in memory that several worker processes of one node map - each registers it
+ * in its own process - lets ANY of their GPUs onboard a block over its own PCIe link: the decode GPU fetches part of a
+ * prefill worker's host-resident blocks itself while the prefill GPU relays the rest over NVLink
+ * (dynamo_exp_b200/shared_host.py, bench.py --gpus N e2e). The reference pins host KV storage per process
+ * (kv/storage.rs:91-101 cuda_malloc_host); this is the counterpart for memory it did not allocate.
+ * kvdp_host_unregister before unmapping. */
+int kvdp_host_register(void* ptr, size_t bytes);
+int kvdp_host_unregister(void* ptr);
+
 /* ---- peers (replaces nixl_agent.register_memory / add_remote_agent metadata exchange, patch:1158-1186,1427-1436) */
 #define KVDP_IPC_HANDLE_BYTES 64
 int kvdp_peer_enable(int32_t device, int32_t peer_device);            /* same-process peers */

@@ -87,6 +87,8 @@ extern "C" {
     pub fn kvdp_stream_synchronize(stream: *mut c_void) -> c_int;
     pub fn kvdp_stream_wait_flag(stream: *mut c_void, flag: *mut u32, value: u32) -> c_int;
     pub fn kvdp_flag_cas64(addr: *mut u64, expected: u64, desired: u64, old: *mut u64, device: i32) -> c_int;
+    pub fn kvdp_host_register(ptr: *mut c_void, bytes: usize) -> c_int;
+    pub fn kvdp_host_unregister(ptr: *mut c_void) -> c_int;
     pub fn kvdp_peer_enable(device: i32, peer_device: i32) -> c_int;
     pub fn kvdp_ipc_export(device_ptr: *mut c_void, handle: *mut u8) -> c_int;
     pub fn kvdp_ipc_export_range(device_ptr: *mut c_void, handle: *mut u8, offset: *mut u64) -> c_int;

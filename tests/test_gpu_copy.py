@@ -759,3 +759,87 @@ def test_copy_stream_dma_runs_in_pieces(gpu, oracle, piece_kib):
         assert L.copy_stream_destroy(cs) == 0
     finally:
         gpu.set_option("host_dma_piece_kib", 8192)
+
+
+def test_copy_stream_on_a_node_shared_registered_host_region(gpu, oracle):
+    """kvdp_host_register: a memfd mapping registered with CUDA behaves like cuda_malloc_host memory for the CopyStream
+    (copy-engine path on host-side runs, zero-copy kernel on scattered ids), in the process that created it and in a second
+    process that opened and registered the same memory (dynamo_exp_b200/shared_host.py). The second process onboards from the
+    first half of the region and offloads into the second half; this process checks both against the oracle."""
+    import os
+    import subprocess
+    import sys
+
+    from dynamo_exp_b200.shared_host import SharedHostRegion
+    L = gpu.lib()
+    layers, nh, nd, suffix, elem = 2, 48, 40, 64 * 1024, 2
+    chunk = suffix * elem
+    layer_bytes = 2 * nh * chunk
+    region = SharedHostRegion.create(2 * layers * layer_bytes)
+    try:
+        arr = region.array()
+        arr[:layers * layer_bytes] = payload(layers * layer_bytes, 4100)
+        src_np = [arr[l * layer_bytes:(l + 1) * layer_bytes].copy() for l in range(layers)]
+        dev = [DevBuf(gpu, 2 * nd * chunk) for _ in range(layers)]
+        rng = np.random.Generator(np.random.PCG64(91))
+        for case, h_ids in (("runs", np.concatenate([np.arange(4, 20), np.arange(30, 46)])),
+                            ("scattered", rng.permutation(nh)[:32])):
+            h_ids = h_ids.astype(np.int32)[rng.permutation(32)].copy()
+            d_ids = rng.permutation(nd)[:32].astype(np.int32)
+            cs = C.c_void_p()
+            assert L.copy_stream_create(C.byref(cs), layers, 32) == 0
+            assert L.copy_stream_prepare_block_ids(cs, h_ids.ctypes.data, d_ids.ctypes.data, 32) == 0
+            for l in range(layers):
+                assert L.copy_stream_memcpy(cs, C.c_void_p(region.ptr + l * layer_bytes), dev[l].ptr, 2, suffix, elem,
+                                            nh, nd) == 0, gpu.last_error()
+            assert L.copy_stream_sync(cs) == 0
+            want = [np.zeros(2 * nd * chunk, dtype=np.uint8) for _ in range(layers)]
+            oracle.copy_blocks_layers(src_np, want, h_ids, d_ids, 2, nh, nd, suffix, elem)
+            for l in range(layers):
+                got = dev[l].download().reshape(2, nd, chunk)[:, d_ids]
+                assert np.array_equal(got, want[l].reshape(2, nd, chunk)[:, d_ids]), (case, l)
+            assert L.copy_stream_destroy(cs) == 0
+        # second process: open + register, onboard blocks 0..31 of the first half, offload them into the second half
+        root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        code = """
+import ctypes as C, sys
+sys.path.insert(0, %r)
+import numpy as np
+from dynamo_exp_b200 import _lib as lib
+from dynamo_exp_b200.shared_host import SharedHostRegion
+L = lib.lib()
+layers, nh, nd, suffix, elem = %d, %d, %d, %d, %d
+chunk = suffix * elem
+layer_bytes = 2 * nh * chunk
+r = SharedHostRegion.open(%r)
+dev = []
+for l in range(layers):
+    p = C.c_void_p()
+    lib.check(L.kvdp_device_alloc(C.byref(p), 2 * nd * chunk, 0))
+    dev.append(p)
+h = np.arange(32, dtype=np.int32)
+d = np.arange(32, dtype=np.int32)[::-1].copy()
+h2 = (np.arange(32, dtype=np.int32) + 16).copy()
+cs = C.c_void_p()
+assert L.copy_stream_create(C.byref(cs), layers, 32) == 0
+lib.check(L.copy_stream_prepare_block_ids(cs, h.ctypes.data, d.ctypes.data, 32))
+for l in range(layers):
+    lib.check(L.copy_stream_memcpy(cs, C.c_void_p(r.ptr + l * layer_bytes), dev[l], 2, suffix, elem, nh, nd))
+lib.check(L.copy_stream_prepare_block_ids(cs, d.ctypes.data, h2.ctypes.data, 32))
+for l in range(layers):
+    lib.check(L.copy_stream_memcpy(cs, dev[l], C.c_void_p(r.ptr + (layers + l) * layer_bytes), 2, suffix, elem, nd, nh))
+lib.check(L.copy_stream_sync(cs))
+L.copy_stream_destroy(cs)
+r.close()
+print("ok")
+""" % (root, layers, nh, nd, suffix, elem, region.handle())
+        out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-2000:]
+        for l in range(layers):
+            a = arr[l * layer_bytes:(l + 1) * layer_bytes].reshape(2, nh, chunk)
+            b = arr[(layers + l) * layer_bytes:(layers + l + 1) * layer_bytes].reshape(2, nh, chunk)
+            assert np.array_equal(b[:, 16:48], a[:, 0:32]), l      # host block i went to host block i + 16
+            assert not b[:, :16].any()
+        del arr, a, b
+    finally:
+        region.close()

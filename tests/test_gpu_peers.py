@@ -158,3 +158,52 @@ def test_notifications_across_gpus_two_senders_and_two_receivers(two_gpus):
         assert c.get_new_notifs() == {s: want[(name, s)] for s in ("prefill-a:0", "prefill-b:0")}
     for c in pa + pb + d1 + d2:
         c.shutdown()
+
+
+def test_onboard_from_a_shared_host_region_over_both_gpus_links(two_gpus, oracle):
+    """bench.py --gpus N e2e, --e2e-links both: host blocks in a registered shared region reach the decode GPU's cache over
+    two PCIe links at once - GPU 0's CopyStream carries request 0 (copy engines into its staging, kernel stores into GPU 1's
+    memory over NVLink), GPU 1's own CopyStream fetches request 1. Every byte of the decode cache against the oracle."""
+    import torch
+
+    from dynamo_exp_b200.shared_host import SharedHostRegion, split_for_links
+    gpu = two_gpus
+    lib = gpu.lib()
+    layers, nh, nd, suffix, elem, per_req = 3, 64, 48, 64 * 1024, 2, 16
+    chunk = suffix * elem
+    layer_bytes = 2 * nh * chunk
+    region = SharedHostRegion.create(layers * layer_bytes)
+    try:
+        arr = region.array()
+        arr[:] = payload(arr.size, 5150)
+        src_np = [arr[l * layer_bytes:(l + 1) * layer_bytes].copy() for l in range(layers)]
+        cache = [DevBuf(gpu, 2 * nd * chunk, 1) for _ in range(layers)]
+        for c in cache:
+            c.upload(np.zeros(c.nbytes, dtype=np.uint8))
+        rng = np.random.Generator(np.random.PCG64(8))
+        h_ids = np.concatenate([np.arange(8, 24), np.arange(40, 56)]).astype(np.int32)
+        d_ids = rng.permutation(nd)[:2 * per_req].astype(np.int32)
+        streams = []
+        for link, (r0, r1) in enumerate(split_for_links(2, 2)):
+            torch.cuda.set_device(link)
+            cs = C.c_void_p()
+            assert lib.copy_stream_create(C.byref(cs), layers, per_req) == 0
+            streams.append(cs)
+            h = h_ids[r0 * per_req:r1 * per_req].copy()
+            d = d_ids[r0 * per_req:r1 * per_req].copy()
+            assert lib.copy_stream_prepare_block_ids(cs, h.ctypes.data, d.ctypes.data, len(h)) == 0
+            for l in range(layers):
+                assert lib.copy_stream_memcpy(cs, C.c_void_p(region.ptr + l * layer_bytes), cache[l].ptr, 2, suffix, elem,
+                                              nh, nd) == 0, gpu.last_error()
+        for cs in streams:
+            assert lib.copy_stream_sync(cs) == 0
+            assert lib.copy_stream_destroy(cs) == 0
+        torch.cuda.set_device(0)
+        want = [np.zeros(2 * nd * chunk, dtype=np.uint8) for _ in range(layers)]
+        oracle.copy_blocks_layers(src_np, want, h_ids, d_ids, 2, nh, nd, suffix, elem)
+        for l in range(layers):
+            assert np.array_equal(cache[l].download(), want[l]), l
+        del arr
+    finally:
+        torch.cuda.set_device(0)
+        region.close()
