@@ -70,8 +70,8 @@ def parse_args():
     ap.add_argument("--e2e-path", default="dma", choices=["dma", "kernel"],
                     help="N>1 e2e leg, prefill side: dma = legacy CopyStream (copy engines into HBM staging + push kernel), "
                          "kernel = one zero-copy kernel reading host memory")
-    ap.add_argument("--e2e-links", default="both", choices=["both", "prefill"],
-                    help="N>1 e2e leg: both = the prefill side's host blocks live in memory both workers of a pair map and "
+    ap.add_argument("--e2e-links", default="auto", choices=["auto", "both", "prefill"],
+                    help="N>1 e2e leg: auto = time both settings, headline the faster; both = the prefill side's host blocks live in memory both workers of a pair map and "
                          "pin, the decode GPU fetches half of each step over its own PCIe link; prefill = the prefill GPU's "
                          "link carries everything")
     ap.add_argument("--no-reshard", action="store_true", help="N>1: skip the Llama-3-70B TP reshard legs (config 3)")
