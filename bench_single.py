@@ -691,7 +691,7 @@ def run_single(args):
     del setup
     torch.cuda.empty_cache()
     if not args.no_e2e:
-        line["e2e"] = e2e_legacy(torch, lib, args, min(args.steps, 8), 2)
+        line["e2e"] = e2e_legacy(torch, lib, args, min(args.steps, 8), max(4, min(args.warmup, 8)))
     if not args.no_e2e:
         line["host_tier"] = host_tier_bench(torch, lib)
         torch.cuda.empty_cache()
