@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import ctypes as C
 import json
+import os
 
 import numpy as np
 
@@ -197,14 +198,35 @@ def run_multi(args, rank, local_rank, world):
         n_req_e = nh // BLOCKS_PER_REQ
         use = {"links": links}                        # links in use by the leg being timed
         host_layer_bytes = 2 * nhc * CHUNK
-        region, handles_e = None, [None] * world
+        region, handles_e, links_fallback = None, [None] * world, None
         if links == 2:
+            # every rank must agree: if one cannot create / open / register the shared region (another pid namespace, a
+            # locked-memory limit), all go back to one link per pair with cuda_malloc_host memory and the line says so
+            err = None
             if is_prefill:
-                region = SharedHostRegion.create(L8B * host_layer_bytes)
-            dist.all_gather_object(handles_e, region.handle() if is_prefill else None)
+                try:
+                    if os.environ.get("KVDP_BENCH_NO_SHARED_HOST"):      # exercises the fallback below
+                        raise RuntimeError("disabled by KVDP_BENCH_NO_SHARED_HOST")
+                    region = SharedHostRegion.create(L8B * host_layer_bytes)
+                except Exception as e:  # noqa: BLE001
+                    err = "create: %s" % e
+            dist.all_gather_object(handles_e, region.handle() if region is not None else None)
             if not is_prefill:
-                region = SharedHostRegion.open(handles_e[partner])
-            dist.barrier()
+                try:
+                    if handles_e[partner] is None:
+                        raise RuntimeError("the prefill side has no region")
+                    region = SharedHostRegion.open(handles_e[partner])
+                except Exception as e:  # noqa: BLE001
+                    err = "open: %s" % e
+            errs = [None] * world
+            dist.all_gather_object(errs, err)
+            if any(e_ is not None for e_ in errs):
+                links_fallback = "; ".join("rank %d %s" % (i_, e_) for i_, e_ in enumerate(errs) if e_)
+                if region is not None:
+                    region.close()
+                    region = None
+                links = 1
+                use["links"] = 1
 
         def step_ids(pair_seed, k):
             """The step's (host ids, decode-cache ids), the same on both workers of a pair."""
@@ -338,6 +360,7 @@ def run_multi(args, rank, local_rank, world):
                       % ("; with links=both the decode GPU fetches half of each step's requests itself over its own "
                          "PCIe link" if links == 2 else ""),
                "links": "both" if links == 2 else "prefill",
+               "links_fallback": links_fallback,
                "onboard_GBps_by_links": {("both" if n_ == 2 else "prefill"): P * nh * BLOCK_BYTES * k_e / t_ / GB
                                          for n_, t_ in sec_by_links.items()},
                "links_note": "--e2e-links auto times the onboard leg with the decode GPU's own link helping (both) and "
