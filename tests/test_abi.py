@@ -63,6 +63,14 @@ def test_loads_and_reports_without_gpu(kvlib):
     assert b"unknown option" in L.kvdp_last_error()
     assert L.kvdp_set_option(b"copy_path", 7) == kvlib.KVDP_EINVAL
     assert L.kvdp_get_option(b"copy_path") == 0
+    # host-side tunables: defaults, round trip, range checks
+    assert L.kvdp_get_option(b"host_dma_piece_kib") == 8192
+    assert L.kvdp_set_option(b"host_dma_piece_kib", 0) == 0 and L.kvdp_get_option(b"host_dma_piece_kib") == 0
+    assert L.kvdp_set_option(b"host_dma_piece_kib", -1) == kvlib.KVDP_EINVAL
+    assert L.kvdp_set_option(b"host_dma_piece_kib", 8192) == 0
+    # registering host memory needs a CUDA context: without a GPU it must fail with an error, not crash; NULL is EINVAL
+    assert L.kvdp_host_register(None, 4096) == kvlib.KVDP_EINVAL
+    assert L.kvdp_host_unregister(None) == kvlib.KVDP_EINVAL
 
 
 def test_oracle_is_not_linked_or_imported_by_the_product():
